@@ -1,0 +1,670 @@
+// dwls_capi.cu — C-ABI of libdwls_b200.so (declared in include/dwls_b200.h): context, workspace,
+// kernel orchestration for DisparityWLSFilter::filter and fastGlobalSmootherFilter.
+// Reference orchestration being replaced: modules/ximgproc/src/disparity_filters.cpp:219-298 and
+// modules/ximgproc/src/fgs_filter.cpp:141-233.  There is no CPU path in this file.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+
+#include "../../include/dwls_b200.h"
+#include "dwls_resize.cuh"
+
+using namespace dwls;
+
+struct dwls_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;                         // second lane of the pipelined host-batch entry point
+    std::string err;
+    int64_t launches = 0;
+    int group_frames = 0;
+    float* lut = nullptr; float lut_sigma = -1.f;           // per-sigma LUT cache (fgs_filter.cpp:150-154)
+    void* ws = nullptr; size_t ws_bytes = 0;                // solver workspace (grow-only)
+    void* stage = nullptr; size_t stage_bytes = 0;          // device staging of the host entry points
+};
+
+static std::string g_create_err;
+
+#define CK(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess) {                                                                     \
+            char b_[512];                                                                            \
+            snprintf(b_, sizeof b_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            ctx->err = b_;                                                                           \
+            return DWLS_CUDA_ERROR;                                                                  \
+        }                                                                                            \
+    } while (0)
+
+static dwls_status fail(dwls_ctx* ctx, dwls_status s, const char* msg) { if (ctx) ctx->err = msg; return s; }
+
+static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+static inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+static dwls_status ensure(dwls_ctx* ctx, void** p, size_t* have, size_t need)
+{
+    if (*have >= need) return DWLS_OK;
+    if (*p) { CK(cudaStreamSynchronize(ctx->stream)); CK(cudaFree(*p)); *p = nullptr; *have = 0; }
+    CK(cudaMalloc(p, need));
+    *have = need;
+    return DWLS_OK;
+}
+
+extern "C" {
+
+void dwls_default_params(dwls_params* p)
+{
+    if (!p) return;
+    p->lambda = 8000.0; p->sigma_color = 1.0; p->lrc_thresh = 24; p->disc_radius = 5;       // disparity_filters.cpp:154-155, 215
+    p->left_offset = p->right_offset = p->top_offset = p->bottom_offset = 0;
+    p->use_confidence = 1; p->lambda_attenuation = 0.25; p->num_iter = 3;                   // edge_filter.hpp:393
+}
+
+const char* dwls_version(void) { return "dwls_b200 0.1 (sm_100a)"; }
+
+dwls_status dwls_ctx_create(int device, dwls_ctx** out)
+{
+    if (!out) return DWLS_BAD_ARG;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        g_create_err = std::string("no CUDA device: ") + cudaGetErrorString(e) + " — this library has no CPU fallback";
+        return DWLS_CUDA_ERROR;
+    }
+    if (device < 0 || device >= n) { g_create_err = "device index out of range"; return DWLS_BAD_ARG; }
+    dwls_ctx* ctx = new dwls_ctx();
+    ctx->device = device;
+    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        g_create_err = std::string("cudaSetDevice/cudaStreamCreate: ") + cudaGetErrorString(e);
+        delete ctx;
+        return DWLS_CUDA_ERROR;
+    }
+    *out = ctx;
+    return DWLS_OK;
+}
+
+void dwls_ctx_destroy(dwls_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
+    if (ctx->stream2) { cudaStreamSynchronize(ctx->stream2); cudaStreamDestroy(ctx->stream2); }
+    cudaFree(ctx->lut); cudaFree(ctx->ws); cudaFree(ctx->stage);
+    delete ctx;
+}
+
+const char* dwls_last_error(const dwls_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+int64_t dwls_kernel_launches(const dwls_ctx* ctx) { return ctx ? ctx->launches : 0; }
+dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames)
+{
+    if (!ctx || frames < 0) return DWLS_BAD_ARG;
+    ctx->group_frames = frames;
+    return DWLS_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// shared pieces
+// ---------------------------------------------------------------------------------------------
+static const int LUT_LEVELS = 3 * 256 * 256;
+
+static dwls_status ensure_lut(dwls_ctx* ctx, float sigma, cudaStream_t st)
+{
+    if (!ctx->lut) CK(cudaMalloc(&ctx->lut, sizeof(float) * LUT_LEVELS));
+    if (ctx->lut_sigma != sigma) {
+        lut_kernel<<<(LUT_LEVELS + 255) / 256, 256, 0, st>>>(ctx->lut, LUT_LEVELS, sigma);
+        CK(cudaGetLastError());
+        ctx->launches++;
+        ctx->lut_sigma = sigma;
+    }
+    return DWLS_OK;
+}
+
+struct SolvePlan { int hK; int vM, vCols, vK; };
+
+static bool plan_solver(int w, int h, SolvePlan* p)
+{
+    p->hK = round_up((w + HM - 1) / HM, 32);
+    if (p->hK > 1024) return false;
+    if (h <= 9 * 128) { p->vM = 9; p->vCols = 8; }
+    else if (h <= 17 * 128) { p->vM = 17; p->vCols = 4; }
+    else if (h <= 17 * 256) { p->vM = 17; p->vCols = 2; }
+    else return false;
+    p->vK = round_up((h + p->vM - 1) / p->vM, 32);
+    return true;
+}
+
+template <int S>
+static dwls_status launch_h(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
+{
+    const size_t smem = sizeof(float) * (4 + 2 * S) * l2pad_size(pl.hK);
+    if (pl.hK <= 256) hsolve_kernel<S, 256><<<dim3(a.h, frames), pl.hK, smem, st>>>(a);
+    else if (pl.hK <= 512) hsolve_kernel<S, 512><<<dim3(a.h, frames), pl.hK, smem, st>>>(a);
+    else hsolve_kernel<S, 1024><<<dim3(a.h, frames), pl.hK, smem, st>>>(a);
+    CK(cudaGetLastError());
+    ctx->launches++;
+    return DWLS_OK;
+}
+
+template <int M, int S, int COLS, int FIN, int MAXT>
+static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
+{
+    const size_t smem = sizeof(float) * COLS * (4 + 2 * S) * l2pad_size(pl.vK);
+    auto k = vsolve_kernel<M, S, COLS, FIN, MAXT>;
+    if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<dim3((a.w + COLS - 1) / COLS, frames), COLS * pl.vK, smem, st>>>(a);
+    CK(cudaGetLastError());
+    ctx->launches++;
+    return DWLS_OK;
+}
+
+template <int S, int FIN>
+static dwls_status launch_v(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
+{
+    if (pl.vM == 9) return launch_v_inst<9, S, 8, FIN, 1024>(ctx, a, pl, frames, st);
+    if (pl.vCols == 4) return launch_v_inst<17, S, 4, FIN, 512>(ctx, a, pl, frames, st);
+    return launch_v_inst<17, S, 2, FIN, 512>(ctx, a, pl, frames, st);
+}
+
+// num_iter x (row pass, column pass, lambda *= attenuation) on S <= 2 planes sharing the weights
+// (fgs_filter.cpp:207-212).  fin != FIN_FLOAT fuses the output conversion into the last column pass.
+static dwls_status run_sweeps(dwls_ctx* ctx, SolveArgs a, const float* chor, const float* cvert, int S, int fin,
+                              const SolvePlan& pl, int frames, double lambda, double att, int num_iter, cudaStream_t st)
+{
+    float lam = (float)lambda;                    // the reference keeps lambda and the attenuation in float (70-71, 146-147)
+    const float fatt = (float)att;
+    for (int n = 0; n < num_iter; ++n) {
+        a.lam = lam;
+        a.weight = chor;
+        dwls_status s = (S == 1) ? launch_h<1>(ctx, a, pl, frames, st) : launch_h<2>(ctx, a, pl, frames, st);
+        if (s) return s;
+        a.weight = cvert;
+        const bool last = (n == num_iter - 1);
+        if (last && fin == FIN_WLS) s = launch_v<2, FIN_WLS>(ctx, a, pl, frames, st);
+        else if (last && fin == FIN_S16) s = launch_v<1, FIN_S16>(ctx, a, pl, frames, st);
+        else s = (S == 1) ? launch_v<1, FIN_FLOAT>(ctx, a, pl, frames, st) : launch_v<2, FIN_FLOAT>(ctx, a, pl, frames, st);
+        if (s) return s;
+        lam *= fatt;
+    }
+    return DWLS_OK;
+}
+
+static dwls_status launch_weights(dwls_ctx* ctx, const uint8_t* guide, int64_t gstep, int64_t gframe, int cn, int w, int h,
+                                  int pitch, float* chor, float* cvert, int64_t wframe, int frames, cudaStream_t st)
+{
+    dim3 grid((pitch + 255) / 256, h, frames);
+    if (cn == 1) weights_kernel<1><<<grid, 256, 0, st>>>(guide, gstep, gframe, w, h, pitch, ctx->lut, chor, cvert, wframe);
+    else weights_kernel<3><<<grid, 256, 0, st>>>(guide, gstep, gframe, w, h, pitch, ctx->lut, chor, cvert, wframe);
+    CK(cudaGetLastError());
+    ctx->launches++;
+    return DWLS_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// DisparityWLSFilter::filter on device buffers
+// ---------------------------------------------------------------------------------------------
+struct Geom {
+    int dw, dh, W, H, vcn;
+    bool same;
+    float resize_factor;
+    int rx, ry, rw, rh, rrx;        // disparity-resolution ROI and its mirror
+    int fx, fy, fw, fh;             // ROI at view resolution
+    int pitch;                      // solver plane pitch (floats)
+    SolvePlan plan;
+};
+
+// ROI rules of disparity_filters.cpp:224-233, 202-203, 245-246; returns BAD_SIZE where cv::Mat(m, roi) would assert
+static dwls_status make_geom(dwls_ctx* ctx, int dw, int dh, int W, int H, int vcn, const int* roi_in, const dwls_params* p, Geom* g)
+{
+    g->dw = dw; g->dh = dh; g->W = W; g->H = H; g->vcn = vcn;
+    g->same = (dw == W && dh == H);
+    g->resize_factor = g->same ? 1.0f : dw / (float)W;
+    if (roi_in && roi_in[2] * roi_in[3] != 0) { g->rx = roi_in[0]; g->ry = roi_in[1]; g->rw = roi_in[2]; g->rh = roi_in[3]; }
+    else { g->rx = p->left_offset; g->ry = p->top_offset; g->rw = dw - p->left_offset - p->right_offset; g->rh = dh - p->top_offset - p->bottom_offset; }
+    if (g->rx < 0 || g->ry < 0 || g->rw <= 0 || g->rh <= 0 || g->rx + g->rw > dw || g->ry + g->rh > dh)
+        return fail(ctx, DWLS_BAD_SIZE, "ROI does not fit inside the disparity map");
+    g->rrx = dw - (g->rx + g->rw);
+    if (g->same) { g->fx = g->rx; g->fy = g->ry; g->fw = g->rw; g->fh = g->rh; }
+    else {
+        const float x_ratio = W / (float)dw, y_ratio = H / (float)dh;
+        g->fx = (int)(g->rx * x_ratio); g->fy = (int)(g->ry * y_ratio); g->fw = (int)(g->rw * x_ratio); g->fh = (int)(g->rh * y_ratio);
+        if (g->fx < 0 || g->fy < 0 || g->fw <= 0 || g->fh <= 0 || g->fx + g->fw > W || g->fy + g->fh > H)
+            return fail(ctx, DWLS_BAD_SIZE, "upscaled ROI does not fit inside the view");
+    }
+    g->pitch = round_up(g->fw, 8);
+    if (!plan_solver(g->fw, g->fh, &g->plan)) return fail(ctx, DWLS_UNSUPPORTED, "ROI larger than 8192 x 4352 is not supported by the on-chip solver");
+    return DWLS_OK;
+}
+
+static dwls_status check_params(dwls_ctx* ctx, const dwls_params* p)
+{
+    if (!p) return fail(ctx, DWLS_BAD_ARG, "params is NULL");
+    if (!(p->lambda >= 0) || !(p->sigma_color >= 0) || p->num_iter < 1)                       // fgs_filter.cpp:143
+        return fail(ctx, DWLS_BAD_ARG, "lambda >= 0, sigma_color >= 0 and num_iter >= 1 are required");
+    if (p->use_confidence && (p->disc_radius < 0 || p->disc_radius > 32)) return fail(ctx, DWLS_UNSUPPORTED, "depth discontinuity radius must be in [0, 32]");
+    return DWLS_OK;
+}
+
+// per-frame workspace layout (floats): chor | cvert | plane0 | plane1 | conf_r | conf_lo
+struct WsLayout { size_t plane, confr, conflo, per_frame; int cr_pitch; };
+static WsLayout ws_layout(const Geom& g, bool use_conf)
+{
+    WsLayout l;
+    l.plane = (size_t)g.pitch * g.fh;
+    l.cr_pitch = round_up(g.rw, 4);
+    l.confr = use_conf ? (size_t)l.cr_pitch * g.rh : 0;
+    l.conflo = (use_conf && !g.same) ? (size_t)g.dw * g.dh : 0;
+    l.per_frame = 4 * l.plane + l.confr + l.conflo;
+    return l;
+}
+
+static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int nf, const Geom& g, const dwls_params* p,
+                                 uint8_t* mask, int64_t mask_step, bool mask_only, cudaStream_t st, float* ws_base = nullptr)
+{
+    const bool conf = p->use_confidence != 0;
+    const WsLayout L = ws_layout(g, conf);
+    float* base = ws_base ? ws_base : (float*)ctx->ws;
+    float* chor = base; float* cvert = chor + (size_t)nf * L.plane;
+    float* p0 = cvert + (size_t)nf * L.plane; float* p1 = p0 + (size_t)nf * L.plane;
+    float* confr = p1 + (size_t)nf * L.plane; float* conflo = confr + (size_t)nf * L.confr;
+
+    const int16_t* dl = (const int16_t*)((const uint8_t*)b->disp_left + (size_t)f0 * b->dl_frame);
+    const int16_t* dr = b->disp_right ? (const int16_t*)((const uint8_t*)b->disp_right + (size_t)f0 * b->dr_frame) : nullptr;
+    const uint8_t* view = b->view ? b->view + (size_t)f0 * b->view_frame : nullptr;
+    int16_t* out = b->out ? (int16_t*)((uint8_t*)b->out + (size_t)f0 * b->out_frame) : nullptr;
+    float* cexp = b->conf ? (float*)((uint8_t*)b->conf + (size_t)f0 * b->conf_frame) : nullptr;
+
+    if (conf) {
+        ConfArgs a;
+        memset(&a, 0, sizeof a);
+        a.dl = dl; a.dl_step = b->dl_step / 2; a.dl_frame = b->dl_frame / 2;
+        a.dr = dr; a.dr_step = b->dr_step / 2; a.dr_frame = b->dr_frame / 2;
+        a.dw = g.dw; a.dh = g.dh; a.rx = g.rx; a.ry = g.ry; a.rw = g.rw; a.rh = g.rh; a.rrx = g.rrx;
+        a.radius = p->disc_radius;
+        const int k = 2 * p->disc_radius + 1;
+        a.scale_d = 1.0 / (k * k); a.scale_f = (float)a.scale_d;
+        a.roll_off = 0.001f / (g.resize_factor * g.resize_factor);                             // 156, 359
+        a.thresh = (int)(g.resize_factor * p->lrc_thresh);                                     // 318
+        a.conf_r = confr; a.cr_frame = L.confr; a.cr_pitch = L.cr_pitch;
+        if (g.same) { a.conf = cexp; a.conf_step = b->conf_step / 4; a.conf_frame = b->conf_frame / 4; a.plane_dc = p0; a.plane_c = p1; }
+        else { a.conf = conflo; a.conf_step = g.dw; a.conf_frame = L.conflo; a.plane_dc = nullptr; a.plane_c = nullptr; }
+        if (mask_only) { a.conf = nullptr; a.plane_dc = nullptr; a.plane_c = nullptr; }
+        a.p_frame = L.plane; a.pitch = g.pitch;
+        a.mask = mask; a.mask_step = mask_step;
+        const size_t smem = sizeof(int16_t) * (CT_W + 2 * a.radius) * (CT_H + 2 * a.radius);
+        conf_kernel<false><<<dim3((g.rw + CT_W - 1) / CT_W, (g.rh + CT_H - 1) / CT_H, nf), dim3(CT_W, CT_H), smem, st>>>(a);
+        CK(cudaGetLastError());
+        conf_kernel<true><<<dim3((g.dw + CT_W - 1) / CT_W, (g.dh + CT_H - 1) / CT_H, nf), dim3(CT_W, CT_H), smem, st>>>(a);
+        CK(cudaGetLastError());
+        ctx->launches += 2;
+        if (mask_only) return DWLS_OK;
+    }
+    if (!g.same) {
+        UpArgs u;
+        memset(&u, 0, sizeof u);
+        u.disp = dl; u.d_step = b->dl_step / 2; u.d_frame = b->dl_frame / 2;
+        u.conf_lo = conf ? conflo : nullptr; u.cl_step = g.dw; u.cl_frame = L.conflo;
+        u.dw = g.dw; u.dh = g.dh; u.W = g.W; u.H = g.H;
+        u.scale_x = 1.0 / ((double)g.W / g.dw); u.scale_y = 1.0 / ((double)g.H / g.dh);
+        u.x_ratio = g.W / (float)g.dw;
+        u.fx = g.fx; u.fy = g.fy; u.fw = g.fw; u.fh = g.fh;
+        u.conf = conf ? cexp : nullptr; u.conf_step = b->conf_step / 4; u.conf_frame = b->conf_frame / 4;
+        u.plane_dc = p0; u.plane_c = conf ? p1 : nullptr; u.p_frame = L.plane; u.pitch = g.pitch;
+        upscale_prep_kernel<<<dim3((g.W + 255) / 256, g.H, nf), 256, 0, st>>>(u);
+        CK(cudaGetLastError());
+        ctx->launches++;
+    } else if (!conf) {
+        prep_noconf_kernel<<<dim3((g.fw + 255) / 256, g.fh, nf), 256, 0, st>>>(dl + (size_t)g.fy * (b->dl_step / 2) + g.fx, b->dl_step / 2,
+                                                                            b->dl_frame / 2, g.fw, g.fh, p0, L.plane, g.pitch);
+        CK(cudaGetLastError());
+        ctx->launches++;
+    }
+    fill_outside_kernel<<<dim3((g.W + 255) / 256, g.H, nf), 256, 0, st>>>(out, b->out_step / 2, b->out_frame / 2, g.W, g.H, g.fx, g.fy, g.fw, g.fh);
+    CK(cudaGetLastError());
+    ctx->launches++;
+    dwls_status s = launch_weights(ctx, view + (size_t)g.fy * b->view_step + (size_t)g.fx * g.vcn, b->view_step, b->view_frame, g.vcn,
+                                   g.fw, g.fh, g.pitch, chor, cvert, L.plane, nf, st);
+    if (s) return s;
+    SolveArgs a;
+    memset(&a, 0, sizeof a);
+    a.w_frame = L.plane; a.p_frame = L.plane; a.pitch = g.pitch; a.w = g.fw; a.h = g.fh;
+    a.in[0] = p0; a.out[0] = p0; a.in[1] = p1; a.out[1] = p1;
+    a.out16 = out + (size_t)g.fy * (b->out_step / 2) + g.fx; a.out16_step = b->out_step / 2; a.out16_frame = b->out_frame / 2;
+    return run_sweeps(ctx, a, chor, cvert, conf ? 2 : 1, conf ? FIN_WLS : FIN_S16, g.plan, nf, p->lambda, p->lambda_attenuation, p->num_iter, st);
+}
+
+static int pick_group(const dwls_ctx* ctx, size_t per_frame_bytes, int n)
+{
+    if (ctx->group_frames > 0) return ctx->group_frames < n ? ctx->group_frames : n;
+    // default: keep a group's workspace near 1 GiB so launches are large but allocation stays modest
+    size_t g = ((size_t)1 << 30) / (per_frame_bytes ? per_frame_bytes : 1);
+    if (g < 1) g = 1;
+    if (g > 32) g = 32;
+    return (int)(g < (size_t)n ? g : (size_t)n);
+}
+
+static dwls_status validate_batch(dwls_ctx* ctx, const dwls_batch* b, const dwls_params* p)
+{
+    if (!b || b->n_frames <= 0) return fail(ctx, DWLS_BAD_ARG, "empty batch");
+    if (!b->disp_left || b->disp_cols <= 0 || b->disp_rows <= 0) return fail(ctx, DWLS_BAD_ARG, "left disparity map is empty");             // 221
+    if (!b->view || b->view_cols <= 0 || b->view_rows <= 0 || (b->view_channels != 1 && b->view_channels != 3))
+        return fail(ctx, DWLS_BAD_ARG, "left view must be a non-empty CV_8UC1 or CV_8UC3 image");                                            // 222
+    if (p->use_confidence && !b->disp_right) return fail(ctx, DWLS_BAD_ARG, "filtering with confidence requires the right disparity map"); // 262
+    if (!b->out) return fail(ctx, DWLS_BAD_ARG, "output is NULL");
+    if ((b->dl_step | b->dl_frame | b->dr_step | b->dr_frame | b->out_step | b->out_frame) & 1) return fail(ctx, DWLS_BAD_ARG, "CV_16S strides must be even");
+    if ((b->conf_step | b->conf_frame) & 3) return fail(ctx, DWLS_BAD_ARG, "CV_32F strides must be multiples of 4");
+    return DWLS_OK;
+}
+
+extern "C" dwls_status dwls_filter_batch_dev(dwls_ctx* ctx, const dwls_batch* b, const int* roi_in, const dwls_params* p,
+                                             int* roi_out, void* stream)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    dwls_status s = check_params(ctx, p);
+    if (s) return s;
+    if ((s = validate_batch(ctx, b, p))) return s;
+    Geom g;
+    if ((s = make_geom(ctx, b->disp_cols, b->disp_rows, b->view_cols, b->view_rows, b->view_channels, roi_in, p, &g))) {
+        if (roi_out) { roi_out[0] = g.rx; roi_out[1] = g.ry; roi_out[2] = g.rw; roi_out[3] = g.rh; }
+        return s;
+    }
+    if (roi_out) { roi_out[0] = g.rx; roi_out[1] = g.ry; roi_out[2] = g.rw; roi_out[3] = g.rh; }
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    const WsLayout L = ws_layout(g, p->use_confidence != 0);
+    const int G = pick_group(ctx, L.per_frame * sizeof(float), b->n_frames);
+    if ((s = ensure(ctx, &ctx->ws, &ctx->ws_bytes, align256((size_t)G * L.per_frame * sizeof(float))))) return s;
+    if ((s = ensure_lut(ctx, (float)p->sigma_color, st))) return s;
+    for (int f0 = 0; f0 < b->n_frames; f0 += G) {
+        const int nf = (b->n_frames - f0 < G) ? b->n_frames - f0 : G;
+        if ((s = filter_frames(ctx, b, f0, nf, g, p, nullptr, 0, false, st))) return s;
+    }
+    return DWLS_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host-buffer entry points (what a cv::Mat facade calls): stage H2D, run, stage D2H, synchronise
+// ---------------------------------------------------------------------------------------------
+static bool img_ok(const dwls_image* m, int depth, int cn_a, int cn_b)
+{
+    return m && m->data && m->rows > 0 && m->cols > 0 && m->depth == depth && (m->channels == cn_a || m->channels == cn_b);
+}
+static size_t elem_size(int depth) { return depth == DWLS_8U ? 1 : depth == DWLS_16S ? 2 : 4; }
+
+static dwls_status filter_host_impl(dwls_ctx* ctx, const dwls_image* dl, const dwls_image* dr, const dwls_image* view,
+                                    const int* roi_in, const dwls_params* p, dwls_image* out, dwls_image* conf, int* roi_out,
+                                    uint8_t* mask, int64_t mask_step, int mask_view_cols)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    dwls_status s = check_params(ctx, p);
+    if (s) return s;
+    const bool mask_only = mask != nullptr;
+    if (!img_ok(dl, DWLS_16S, 1, 1)) return fail(ctx, DWLS_BAD_ARG, "left disparity map must be a non-empty CV_16SC1 image");          // 221
+    if (!mask_only && !img_ok(view, DWLS_8U, 1, 3)) return fail(ctx, DWLS_BAD_ARG, "left view must be a non-empty CV_8UC1 or CV_8UC3 image"); // 222
+    const bool useconf = p->use_confidence != 0;
+    if (useconf) {
+        if (!img_ok(dr, DWLS_16S, 1, 1)) return fail(ctx, DWLS_BAD_ARG, "right disparity map must be a non-empty CV_16SC1 image");      // 262
+        if (dr->cols != dl->cols || dr->rows != dl->rows) return fail(ctx, DWLS_BAD_ARG, "left and right disparity maps differ in size"); // 263-264
+    }
+    const int dw = dl->cols, dh = dl->rows;
+    const int W = mask_only ? (mask_view_cols > 0 ? mask_view_cols : dw) : view->cols;
+    const int H = mask_only ? (W == dw ? dh : (int)((int64_t)dh * W / dw)) : view->rows;
+    const int vcn = mask_only ? 1 : view->channels;
+    if (!mask_only) {
+        if (!out || !out->data || out->rows != H || out->cols != W || out->depth != DWLS_16S || out->channels != 1)
+            return fail(ctx, DWLS_BAD_ARG, "output must be a caller-allocated CV_16SC1 image of the view size");
+        if (conf && conf->data && (conf->rows != H || conf->cols != W || conf->depth != DWLS_32F || conf->channels != 1))
+            return fail(ctx, DWLS_BAD_ARG, "confidence output must be CV_32FC1 of the view size");
+    }
+    Geom g;
+    s = make_geom(ctx, dw, dh, W, H, vcn, roi_in, p, &g);
+    if (roi_out) { roi_out[0] = g.rx; roi_out[1] = g.ry; roi_out[2] = g.rw; roi_out[3] = g.rh; }
+    if (s) return s;
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const bool want_conf = !mask_only && useconf && conf && conf->data;
+    const size_t b_dl = align256((size_t)dw * dh * 2), b_view = mask_only ? 0 : align256((size_t)W * H * vcn),
+                 b_out = mask_only ? 0 : align256((size_t)W * H * 2), b_conf = want_conf ? align256((size_t)W * H * 4) : 0,
+                 b_mask = mask_only ? align256((size_t)dw * dh) : 0;
+    if ((s = ensure(ctx, &ctx->stage, &ctx->stage_bytes, 2 * b_dl + b_view + b_out + b_conf + b_mask))) return s;
+    uint8_t* d = (uint8_t*)ctx->stage;
+    uint8_t* d_dl = d; uint8_t* d_dr = d_dl + b_dl; uint8_t* d_view = d_dr + b_dl; uint8_t* d_out = d_view + b_view;
+    uint8_t* d_conf = d_out + b_out; uint8_t* d_mask = d_conf + b_conf;
+    CK(cudaMemcpy2DAsync(d_dl, (size_t)dw * 2, dl->data, dl->step, (size_t)dw * 2, dh, cudaMemcpyHostToDevice, st));
+    if (useconf) CK(cudaMemcpy2DAsync(d_dr, (size_t)dw * 2, dr->data, dr->step, (size_t)dw * 2, dh, cudaMemcpyHostToDevice, st));
+    if (!mask_only) CK(cudaMemcpy2DAsync(d_view, (size_t)W * vcn, view->data, view->step, (size_t)W * vcn, H, cudaMemcpyHostToDevice, st));
+    dwls_batch b;
+    memset(&b, 0, sizeof b);
+    b.n_frames = 1;
+    b.disp_left = (const int16_t*)d_dl; b.dl_step = (int64_t)dw * 2;
+    b.disp_right = useconf ? (const int16_t*)d_dr : nullptr; b.dr_step = (int64_t)dw * 2;
+    b.disp_cols = dw; b.disp_rows = dh;
+    b.view = d_view; b.view_step = (int64_t)W * vcn; b.view_cols = W; b.view_rows = H; b.view_channels = vcn;
+    b.out = (int16_t*)d_out; b.out_step = (int64_t)W * 2;
+    b.conf = want_conf ? (float*)d_conf : nullptr; b.conf_step = (int64_t)W * 4;
+    const WsLayout L = ws_layout(g, useconf);
+    if ((s = ensure(ctx, &ctx->ws, &ctx->ws_bytes, align256(L.per_frame * sizeof(float))))) return s;
+    if (mask_only) {
+        if (!useconf) return fail(ctx, DWLS_BAD_ARG, "the LRC mask exists only when filtering with confidence");
+        if ((s = filter_frames(ctx, &b, 0, 1, g, p, d_mask, dw, true, st))) return s;
+        CK(cudaMemcpy2DAsync(mask, mask_step, d_mask, dw, dw, dh, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        return DWLS_OK;
+    }
+    if ((s = ensure_lut(ctx, (float)p->sigma_color, st))) return s;
+    if ((s = filter_frames(ctx, &b, 0, 1, g, p, nullptr, 0, false, st))) return s;
+    CK(cudaMemcpy2DAsync(out->data, out->step, d_out, (size_t)W * 2, (size_t)W * 2, H, cudaMemcpyDeviceToHost, st));
+    if (want_conf) CK(cudaMemcpy2DAsync(conf->data, conf->step, d_conf, (size_t)W * 4, (size_t)W * 4, H, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return DWLS_OK;
+}
+
+extern "C" dwls_status dwls_filter_host(dwls_ctx* ctx, const dwls_image* dl, const dwls_image* dr, const dwls_image* view,
+                                        const int* roi_in, const dwls_params* p, dwls_image* out, dwls_image* conf, int* roi_out)
+{
+    return filter_host_impl(ctx, dl, dr, view, roi_in, p, out, conf, roi_out, nullptr, 0, 0);
+}
+
+extern "C" dwls_status dwls_lrc_mask_host(dwls_ctx* ctx, const dwls_image* dl, const dwls_image* dr, int view_cols, const int* roi_in,
+                                          const dwls_params* p, uint8_t* mask, int64_t mask_step)
+{
+    if (!mask) return fail(ctx, DWLS_BAD_ARG, "mask is NULL");
+    return filter_host_impl(ctx, dl, dr, nullptr, roi_in, p, nullptr, nullptr, nullptr, mask, mask_step, view_cols);
+}
+
+// ---------------------------------------------------------------------------------------------
+// fastGlobalSmootherFilter (fgs_filter.cpp:687-691)
+// ---------------------------------------------------------------------------------------------
+static dwls_status fgs_check(dwls_ctx* ctx, const dwls_image* guide, const dwls_image* src, const dwls_image* dst,
+                             double lambda, double sigma, int num_iter)
+{
+    if (!guide || !guide->data || guide->rows <= 0 || guide->cols <= 0 || !(lambda >= 0) || !(sigma >= 0) || num_iter < 1)
+        return fail(ctx, DWLS_BAD_ARG, "guide must be non-empty, lambda >= 0, sigma_color >= 0, num_iter >= 1");                       // 143
+    if (guide->depth != DWLS_8U || (guide->channels != 1 && guide->channels != 3))
+        return fail(ctx, DWLS_BAD_ARG, "guide must be CV_8UC1 or CV_8UC3");                                                              // 144
+    if (!src || !src->data || src->rows <= 0 || src->cols <= 0 || (src->depth != DWLS_8U && src->depth != DWLS_16S && src->depth != DWLS_32F) ||
+        src->channels < 1 || src->channels > 4)
+        return fail(ctx, DWLS_BAD_ARG, "src must be non-empty CV_8U / CV_16S / CV_32F with at most 4 channels");                        // 184
+    if (src->rows != guide->rows || src->cols != guide->cols)
+        return fail(ctx, DWLS_BAD_SIZE, "Size of the filtered image must be equal to the size of the guide image");                     // 185-189
+    if (!dst || !dst->data || dst->rows != src->rows || dst->cols != src->cols || dst->depth != src->depth || dst->channels != src->channels)
+        return fail(ctx, DWLS_BAD_ARG, "dst must be caller-allocated with the size and type of src");
+    return DWLS_OK;
+}
+
+template <typename T>
+static void launch_unpack(const dwls_image* src, float* planes, size_t plane, int pitch, cudaStream_t st)
+{
+    unpack_kernel<T><<<dim3((src->cols + 255) / 256, src->rows), 256, 0, st>>>((const T*)src->data, src->step, src->cols, src->channels, planes, plane, pitch);
+}
+template <typename T>
+static void launch_pack(const float* planes, size_t plane, int pitch, dwls_image* dst, cudaStream_t st)
+{
+    pack_kernel<T><<<dim3((dst->cols + 255) / 256, dst->rows), 256, 0, st>>>(planes, plane, pitch, dst->cols, dst->channels, (T*)dst->data, dst->step);
+}
+
+// workspace: chor | cvert | up to 4 planes (+ optional export of the weights)
+static dwls_status fgs_dev_impl(dwls_ctx* ctx, const dwls_image* guide, const dwls_image* src, dwls_image* dst, double lambda,
+                                double sigma, double att, int num_iter, cudaStream_t st, float* chor_out, float* cvert_out)
+{
+    const int w = guide->cols, h = guide->rows, pitch = round_up(w, 8);
+    SolvePlan pl;
+    if (!plan_solver(w, h, &pl)) return fail(ctx, DWLS_UNSUPPORTED, "images larger than 8192 x 4352 are not supported by the on-chip solver");
+    const size_t plane = (size_t)pitch * h;
+    const int S = src ? src->channels : 0;
+    dwls_status s;
+    if ((s = ensure(ctx, &ctx->ws, &ctx->ws_bytes, align256((2 + S) * plane * sizeof(float))))) return s;
+    if ((s = ensure_lut(ctx, (float)sigma, st))) return s;
+    float* chor = (float*)ctx->ws; float* cvert = chor + plane; float* planes = cvert + plane;
+    if ((s = launch_weights(ctx, (const uint8_t*)guide->data, guide->step, 0, guide->channels, w, h, pitch, chor, cvert, plane, 1, st))) return s;
+    if (chor_out) {
+        CK(cudaMemcpy2DAsync(chor_out, (size_t)w * 4, chor, (size_t)pitch * 4, (size_t)w * 4, h, cudaMemcpyDeviceToDevice, st));
+        CK(cudaMemcpy2DAsync(cvert_out, (size_t)w * 4, cvert, (size_t)pitch * 4, (size_t)w * 4, h, cudaMemcpyDeviceToDevice, st));
+        return DWLS_OK;
+    }
+    if (src->depth == DWLS_8U) launch_unpack<uint8_t>(src, planes, plane, pitch, st);
+    else if (src->depth == DWLS_16S) launch_unpack<int16_t>(src, planes, plane, pitch, st);
+    else launch_unpack<float>(src, planes, plane, pitch, st);
+    CK(cudaGetLastError());
+    ctx->launches++;
+    // channels are independent solves sharing the weights (fgs_filter.cpp:200-221): two planes per launch
+    for (int c0 = 0; c0 < S; c0 += 2) {
+        const int ns = (S - c0 >= 2) ? 2 : 1;
+        SolveArgs a;
+        memset(&a, 0, sizeof a);
+        a.w_frame = plane; a.p_frame = plane; a.pitch = pitch; a.w = w; a.h = h;
+        for (int k = 0; k < ns; ++k) { a.in[k] = planes + (size_t)(c0 + k) * plane; a.out[k] = planes + (size_t)(c0 + k) * plane; }
+        if ((s = run_sweeps(ctx, a, chor, cvert, ns, FIN_FLOAT, pl, 1, lambda, att, num_iter, st))) return s;
+    }
+    if (dst->depth == DWLS_8U) launch_pack<uint8_t>(planes, plane, pitch, dst, st);
+    else if (dst->depth == DWLS_16S) launch_pack<int16_t>(planes, plane, pitch, dst, st);
+    else launch_pack<float>(planes, plane, pitch, dst, st);
+    CK(cudaGetLastError());
+    ctx->launches++;
+    return DWLS_OK;
+}
+
+extern "C" dwls_status dwls_fgs_dev(dwls_ctx* ctx, const dwls_image* guide, const dwls_image* src, dwls_image* dst, double lambda,
+                                    double sigma, double att, int num_iter, void* stream)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    dwls_status s = fgs_check(ctx, guide, src, dst, lambda, sigma, num_iter);
+    if (s) return s;
+    CK(cudaSetDevice(ctx->device));
+    return fgs_dev_impl(ctx, guide, src, dst, lambda, sigma, att, num_iter, stream ? (cudaStream_t)stream : ctx->stream, nullptr, nullptr);
+}
+
+extern "C" dwls_status dwls_fgs_host(dwls_ctx* ctx, const dwls_image* guide, const dwls_image* src, dwls_image* dst, double lambda,
+                                     double sigma, double att, int num_iter)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    dwls_status s = fgs_check(ctx, guide, src, dst, lambda, sigma, num_iter);
+    if (s) return s;
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int w = guide->cols, h = guide->rows;
+    const size_t grow = (size_t)w * guide->channels, srow = (size_t)w * src->channels * elem_size(src->depth);
+    const size_t b_g = align256(grow * h), b_s = align256(srow * h);
+    if ((s = ensure(ctx, &ctx->stage, &ctx->stage_bytes, b_g + 2 * b_s))) return s;
+    uint8_t* d_g = (uint8_t*)ctx->stage; uint8_t* d_s = d_g + b_g; uint8_t* d_d = d_s + b_s;
+    CK(cudaMemcpy2DAsync(d_g, grow, guide->data, guide->step, grow, h, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpy2DAsync(d_s, srow, src->data, src->step, srow, h, cudaMemcpyHostToDevice, st));
+    dwls_image G = *guide, Sm = *src, D = *dst;
+    G.data = d_g; G.step = (int64_t)grow; Sm.data = d_s; Sm.step = (int64_t)srow; D.data = d_d; D.step = (int64_t)srow;
+    if ((s = fgs_dev_impl(ctx, &G, &Sm, &D, lambda, sigma, att, num_iter, st, nullptr, nullptr))) return s;
+    CK(cudaMemcpy2DAsync(dst->data, dst->step, d_d, srow, srow, h, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return DWLS_OK;
+}
+
+extern "C" dwls_status dwls_fgs_weights_host(dwls_ctx* ctx, const dwls_image* guide, double sigma, float* chor, float* cvert)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    if (!guide || !guide->data || guide->rows <= 0 || guide->cols <= 0 || guide->depth != DWLS_8U || (guide->channels != 1 && guide->channels != 3) ||
+        !(sigma >= 0) || !chor || !cvert)
+        return fail(ctx, DWLS_BAD_ARG, "guide must be non-empty CV_8UC1 / CV_8UC3, sigma_color >= 0");
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int w = guide->cols, h = guide->rows;
+    const size_t grow = (size_t)w * guide->channels, b_g = align256(grow * h), b_w = align256((size_t)w * h * 4);
+    dwls_status s;
+    if ((s = ensure(ctx, &ctx->stage, &ctx->stage_bytes, b_g + 2 * b_w))) return s;
+    uint8_t* d_g = (uint8_t*)ctx->stage; float* d_h = (float*)(d_g + b_g); float* d_v = (float*)(d_g + b_g + b_w);
+    CK(cudaMemcpy2DAsync(d_g, grow, guide->data, guide->step, grow, h, cudaMemcpyHostToDevice, st));
+    dwls_image G = *guide;
+    G.data = d_g; G.step = (int64_t)grow;
+    if ((s = fgs_dev_impl(ctx, &G, nullptr, nullptr, 0.0, sigma, 0.25, 1, st, d_h, d_v))) return s;
+    CK(cudaMemcpyAsync(chor, d_h, (size_t)w * h * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(cvert, d_v, (size_t)w * h * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return DWLS_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// batch of frames in HOST memory (pinned for full speed): two lanes, each with its own stream,
+// staging area and workspace, so the H2D copy of one group overlaps the kernels and the D2H copy
+// of the previous one.  Returns after everything has landed in the host outputs.
+// ---------------------------------------------------------------------------------------------
+extern "C" dwls_status dwls_filter_batch_host(dwls_ctx* ctx, const dwls_batch* hb, const int* roi_in, const dwls_params* p, int* roi_out)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    dwls_status s = check_params(ctx, p);
+    if (s) return s;
+    if ((s = validate_batch(ctx, hb, p))) return s;
+    Geom g;
+    s = make_geom(ctx, hb->disp_cols, hb->disp_rows, hb->view_cols, hb->view_rows, hb->view_channels, roi_in, p, &g);
+    if (roi_out) { roi_out[0] = g.rx; roi_out[1] = g.ry; roi_out[2] = g.rw; roi_out[3] = g.rh; }
+    if (s) return s;
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->stream2) CK(cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+    const bool useconf = p->use_confidence != 0, want_conf = useconf && hb->conf;
+    const int dw = g.dw, dh = g.dh, W = g.W, H = g.H, vcn = g.vcn;
+    const WsLayout L = ws_layout(g, useconf);
+    int G = pick_group(ctx, L.per_frame * sizeof(float), hb->n_frames);
+    if (ctx->group_frames == 0 && G > 8) G = 8;           // smaller groups pipeline better against PCIe
+    const size_t f_dl = align256((size_t)dw * dh * 2), f_view = align256((size_t)W * H * vcn), f_out = align256((size_t)W * H * 2),
+                 f_conf = want_conf ? align256((size_t)W * H * 4) : 0;
+    const size_t lane_stage = (size_t)G * (2 * f_dl + f_view + f_out + f_conf);
+    const size_t lane_ws = align256((size_t)G * L.per_frame * sizeof(float));
+    if ((s = ensure(ctx, &ctx->stage, &ctx->stage_bytes, 2 * lane_stage))) return s;
+    if ((s = ensure(ctx, &ctx->ws, &ctx->ws_bytes, 2 * lane_ws))) return s;
+    if ((s = ensure_lut(ctx, (float)p->sigma_color, ctx->stream))) return s;
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaStream_t lanes[2] = { ctx->stream, ctx->stream2 };
+    int lane = 0;
+    for (int f0 = 0; f0 < hb->n_frames; f0 += G, lane ^= 1) {
+        const int nf = (hb->n_frames - f0 < G) ? hb->n_frames - f0 : G;
+        cudaStream_t st = lanes[lane];
+        uint8_t* d = (uint8_t*)ctx->stage + lane * lane_stage;
+        uint8_t* d_dl = d; uint8_t* d_dr = d_dl + (size_t)G * f_dl; uint8_t* d_view = d_dr + (size_t)G * f_dl;
+        uint8_t* d_out = d_view + (size_t)G * f_view; uint8_t* d_conf = d_out + (size_t)G * f_out;
+        for (int f = 0; f < nf; ++f) {
+            const size_t hf = (size_t)(f0 + f);
+            CK(cudaMemcpy2DAsync(d_dl + f * f_dl, (size_t)dw * 2, (const uint8_t*)hb->disp_left + hf * hb->dl_frame, hb->dl_step, (size_t)dw * 2, dh, cudaMemcpyHostToDevice, st));
+            if (useconf) CK(cudaMemcpy2DAsync(d_dr + f * f_dl, (size_t)dw * 2, (const uint8_t*)hb->disp_right + hf * hb->dr_frame, hb->dr_step, (size_t)dw * 2, dh, cudaMemcpyHostToDevice, st));
+            CK(cudaMemcpy2DAsync(d_view + f * f_view, (size_t)W * vcn, hb->view + hf * hb->view_frame, hb->view_step, (size_t)W * vcn, H, cudaMemcpyHostToDevice, st));
+        }
+        dwls_batch b;
+        memset(&b, 0, sizeof b);
+        b.n_frames = nf;
+        b.disp_left = (const int16_t*)d_dl; b.dl_step = (int64_t)dw * 2; b.dl_frame = (int64_t)f_dl;
+        b.disp_right = useconf ? (const int16_t*)d_dr : nullptr; b.dr_step = (int64_t)dw * 2; b.dr_frame = (int64_t)f_dl;
+        b.disp_cols = dw; b.disp_rows = dh;
+        b.view = d_view; b.view_step = (int64_t)W * vcn; b.view_frame = (int64_t)f_view; b.view_cols = W; b.view_rows = H; b.view_channels = vcn;
+        b.out = (int16_t*)d_out; b.out_step = (int64_t)W * 2; b.out_frame = (int64_t)f_out;
+        b.conf = want_conf ? (float*)d_conf : nullptr; b.conf_step = (int64_t)W * 4; b.conf_frame = (int64_t)f_conf;
+        if ((s = filter_frames(ctx, &b, 0, nf, g, p, nullptr, 0, false, st, (float*)((uint8_t*)ctx->ws + lane * lane_ws)))) return s;
+        for (int f = 0; f < nf; ++f) {
+            const size_t hf = (size_t)(f0 + f);
+            CK(cudaMemcpy2DAsync((uint8_t*)hb->out + hf * hb->out_frame, hb->out_step, d_out + f * f_out, (size_t)W * 2, (size_t)W * 2, H, cudaMemcpyDeviceToHost, st));
+            if (want_conf) CK(cudaMemcpy2DAsync((uint8_t*)hb->conf + hf * hb->conf_frame, hb->conf_step, d_conf + f * f_conf, (size_t)W * 4, (size_t)W * 4, H, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream2));
+    return DWLS_OK;
+}

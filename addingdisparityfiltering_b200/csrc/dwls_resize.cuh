@@ -1,0 +1,100 @@
+// dwls_resize.cuh — half-resolution mode (disparity_filters.cpp:239-247, 268-277): bilinear
+// upscale of the CV_16S disparity (x x_ratio, RNE + saturate) and of the CV_32F confidence to the
+// view size, fused with plane preparation; plus the interleaved <-> planar conversions of the
+// standalone fastGlobalSmootherFilter entry point (fgs_filter.cpp:191-205, 214-232).
+#pragma once
+#include "dwls_stages.cuh"
+
+namespace dwls {
+
+// cv::resize INTER_LINEAR geometry for one destination index (work type float):
+// f = (float)((d+0.5)*scale-0.5); s = floor(f); f -= s.  Horizontal coefficients are zeroed at
+// the borders, vertical source rows are clipped instead.
+struct Lin { int s; float f; };
+__device__ __forceinline__ Lin lin_coeff(int d, double scale, int ssize, bool clamp_coeff)
+{
+    float f = (float)(((double)d + 0.5) * scale - 0.5);
+    int s = (int)floorf(f);
+    f = __fsub_rn(f, (float)s);
+    if (clamp_coeff) {
+        if (s < 0) { f = 0.f; s = 0; }
+        if (s >= ssize - 1) { f = 0.f; s = ssize - 1; }
+    }
+    return { s, f };
+}
+
+template <typename T>
+__device__ __forceinline__ float lin_h(const T* row, Lin cx, int sw)
+{
+    if (cx.s >= sw - 1) return __fmul_rn((float)row[sw - 1], 1.0f);
+    const float a1 = cx.f, a0 = __fsub_rn(1.f, a1);
+    return __fadd_rn(__fmul_rn((float)row[cx.s], a0), __fmul_rn((float)row[cx.s + 1], a1));
+}
+
+struct UpArgs {
+    const int16_t* disp; int64_t d_step, d_frame;     // low-res disparity (elements)
+    const float* conf_lo; int64_t cl_step, cl_frame;  // low-res confidence 0..255 (NULL when !use_confidence)
+    int dw, dh, W, H;
+    double scale_x, scale_y;                          // 1 / (W/dw), 1 / (H/dh)
+    float x_ratio;                                    // W / (float)dw
+    int fx, fy, fw, fh;                               // ROI in view coordinates (245-246 / 275-276)
+    float* conf; int64_t conf_step, conf_frame;       // exported view-size confidence (may be NULL)
+    float* plane_dc; float* plane_c; int64_t p_frame; int pitch;   // plane_c NULL in the no-confidence path
+};
+
+// grid = (ceil(W/256), H, frames).  Only ROI pixels need the disparity; the confidence export
+// needs every pixel.
+__global__ void __launch_bounds__(256) upscale_prep_kernel(const UpArgs a)
+{
+    const int X = blockIdx.x * blockDim.x + threadIdx.x, Y = blockIdx.y, frame = blockIdx.z;
+    if (X >= a.W) return;
+    const bool in_roi = X >= a.fx && X < a.fx + a.fw && Y >= a.fy && Y < a.fy + a.fh;
+    if (!in_roi && !(a.conf && a.conf_lo)) return;
+    const Lin cx = lin_coeff(X, a.scale_x, a.dw, true), cy = lin_coeff(Y, a.scale_y, a.dh, false);
+    const int y0 = min(max(cy.s, 0), a.dh - 1), y1 = min(max(cy.s + 1, 0), a.dh - 1);
+    const float b1 = cy.f, b0 = __fsub_rn(1.f, b1);
+    float cval = 0.f;
+    if (a.conf_lo) {
+        const float* c = a.conf_lo + (size_t)frame * a.cl_frame;
+        const float h0 = lin_h(c + (size_t)y0 * a.cl_step, cx, a.dw), h1 = lin_h(c + (size_t)y1 * a.cl_step, cx, a.dw);
+        cval = __fadd_rn(__fmul_rn(h0, b0), __fmul_rn(h1, b1));
+        if (a.conf) a.conf[(size_t)frame * a.conf_frame + (size_t)Y * a.conf_step + X] = cval;
+    }
+    if (!in_roi) return;
+    const int16_t* d = a.disp + (size_t)frame * a.d_frame;
+    const float h0 = lin_h(d + (size_t)y0 * a.d_step, cx, a.dw), h1 = lin_h(d + (size_t)y1 * a.d_step, cx, a.dw);
+    const int16_t up = cvt_s16(__fadd_rn(__fmul_rn(h0, b0), __fmul_rn(h1, b1)));          // resize -> CV_16S
+    const float dv = (float)cvt_s16(__fmul_rn((float)up, a.x_ratio));                     // disp * x_ratio -> CV_16S (244/273)
+    const size_t po = (size_t)frame * a.p_frame + (size_t)(Y - a.fy) * a.pitch + (X - a.fx);
+    if (a.plane_c) { a.plane_c[po] = cval; a.plane_dc[po] = __fmul_rn(cval, dv); }
+    else a.plane_dc[po] = dv;
+}
+
+// ---- standalone FGS: interleaved source -> float planes, float planes -> interleaved dst ------
+// grid = (ceil(w/256), h), S = channels
+template <typename T>
+__global__ void unpack_kernel(const T* __restrict__ src, int64_t sstep_bytes, int w, int cn,
+                              float* __restrict__ planes, int64_t plane_stride, int pitch)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= w) return;
+    const T* row = (const T*)((const uint8_t*)src + (size_t)i * sstep_bytes) + (size_t)j * cn;
+    for (int ch = 0; ch < cn; ++ch) planes[(size_t)ch * plane_stride + (size_t)i * pitch + j] = (float)row[ch];
+}
+
+template <typename T> __device__ __forceinline__ T cvt_out(float v);
+template <> __device__ __forceinline__ uint8_t cvt_out<uint8_t>(float v) { return cvt_u8(v); }
+template <> __device__ __forceinline__ int16_t cvt_out<int16_t>(float v) { return cvt_s16(v); }
+template <> __device__ __forceinline__ float cvt_out<float>(float v) { return v; }
+
+template <typename T>
+__global__ void pack_kernel(const float* __restrict__ planes, int64_t plane_stride, int pitch, int w, int cn,
+                            T* __restrict__ dst, int64_t dstep_bytes)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= w) return;
+    T* row = (T*)((uint8_t*)dst + (size_t)i * dstep_bytes) + (size_t)j * cn;
+    for (int ch = 0; ch < cn; ++ch) row[ch] = cvt_out<T>(planes[(size_t)ch * plane_stride + (size_t)i * pitch + j]);
+}
+
+}  // namespace dwls

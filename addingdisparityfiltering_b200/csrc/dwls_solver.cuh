@@ -1,0 +1,211 @@
+// dwls_solver.cuh — tridiagonal line solver shared by the row (horizontal) and column (vertical)
+// passes of the Fast Global Smoother (reference: modules/ximgproc/src/fgs_filter.cpp:439-464 row
+// solve, 484-584 column solve).
+//
+// The reference runs Thomas' algorithm serially along each line.  A line of 1080..3840 unknowns
+// is far too long a dependency chain for a GPU thread, so each line is solved by substructuring
+// (Schur complement) in two levels, all on-chip:
+//   level 1  every thread owns M consecutive unknowns in REGISTERS, eliminates its M-1 interior
+//            unknowns (local Thomas with two spike right-hand sides) and emits one row of a
+//            reduced tridiagonal system that couples only the per-thread separators;
+//   level 2  one warp per reduced system repeats the same step on chunks held in shared memory
+//            and is left with a 32-unknown tridiagonal system, one row per lane, which it solves
+//            by warp-shuffle parallel cyclic reduction (5 steps);
+//   fix-up   separators are broadcast back through shared memory and every thread finishes
+//            its interior unknowns with two FMAs per plane.
+// All S planes of a call (d*c and c for the WLS filter, the channels of an FGS source) share
+// the weights, the factorisation and the spikes.
+//
+// System per line (a_j = lam*C[j-1], c_j = lam*C[j], b_j = 1 - a_j - c_j, C <= 0 so b_j >= 1):
+//      a_j u[j-1] + b_j u[j] + c_j u[j+1] = f[j]
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dwls {
+
+// reciprocal of a float known to be a normal number >= 1: MUFU.RCP + one Newton step
+__device__ __forceinline__ float rcp_nr(float x)
+{
+    float r;
+    asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return fmaf(r, fmaf(-x, r, 1.0f), r);
+}
+
+// padded index for level-2 shared arrays (breaks power-of-two lane strides)
+__device__ __forceinline__ int l2pad(int i) { return i + (i >> 5); }
+__host__ __device__ inline int l2pad_size(int n) { return n + (n >> 5) + 1; }
+
+// ---------------------------------------------------------------------------------------------
+// level 1: registers.  On entry c[i] = lam*C of element i, f[s][i] = right-hand sides,
+// aprev = lam*C of the element before the chunk (0 for the first chunk of a line).
+// On exit, for the interior i = 0..M-2:  u_i = f[s][i] - v[i]*U_prev - c[i]*U_own
+// (f holds x, c holds w) and the return values are this chunk's separator row pieces.
+// ---------------------------------------------------------------------------------------------
+template <int M, int S>
+struct Level1Out {
+    float A, B, Fs[S];        // own contributions to reduced row k
+    float dB, Cn, dF[S];      // contributions of this chunk to reduced row k-1 (the previous chunk's)
+};
+
+template <int M, int S>
+__device__ __forceinline__ Level1Out<M, S> level1_reduce(float (&c)[M], float (&f)[S][M], float (&v)[M], float aprev)
+{
+    static_assert(M >= 2, "chunk needs an interior");
+    Level1Out<M, S> o;
+    // separator coefficients before c[] is overwritten
+    const float a_s = c[M - 2], c_s = c[M - 1];
+    const float b_s = 1.0f - a_s - c_s;
+    // forward elimination over the interior
+    float a = aprev, ct_prev = 0.f, vt_prev = 0.f, ft_prev[S];
+#pragma unroll
+    for (int s = 0; s < S; ++s) ft_prev[s] = 0.f;
+#pragma unroll
+    for (int i = 0; i < M - 1; ++i) {
+        const float ci = c[i];
+        const float den = (1.0f - a - ci) - a * ct_prev;
+        const float r = rcp_nr(den);
+        const float ct = ci * r;
+        const float vt = (i == 0) ? a * r : -(a * vt_prev) * r;
+#pragma unroll
+        for (int s = 0; s < S; ++s) { const float ft = (f[s][i] - a * ft_prev[s]) * r; f[s][i] = ft; ft_prev[s] = ft; }
+        c[i] = ct; v[i] = vt;
+        ct_prev = ct; vt_prev = vt;
+        a = ci;
+    }
+    // backward substitution: x (in f), v, w (in c)
+    float w_next = c[M - 2], v_next = v[M - 2];      // w_{M-2} = ct_{M-2}
+#pragma unroll
+    for (int i = M - 3; i >= 0; --i) {
+        const float ct = c[i];
+#pragma unroll
+        for (int s = 0; s < S; ++s) f[s][i] = fmaf(-ct, f[s][i + 1], f[s][i]);
+        v_next = fmaf(-ct, v_next, v[i]); v[i] = v_next;
+        w_next = -ct * w_next; c[i] = w_next;
+    }
+    // separator row k:  A U_{k-1} + B U_k + C U_{k+1} = F ; own part uses the last interior element
+    o.A = -a_s * v[M - 2];
+    o.B = b_s - a_s * c[M - 2];
+#pragma unroll
+    for (int s = 0; s < S; ++s) o.Fs[s] = f[s][M - 1] - a_s * f[s][M - 2];
+    // what this chunk's first interior element contributes to the PREVIOUS separator row (its c_s = aprev)
+    o.dB = -aprev * v[0];
+    o.Cn = -aprev * c[0];
+#pragma unroll
+    for (int s = 0; s < S; ++s) o.dF[s] = -aprev * f[s][0];
+    return o;
+}
+
+template <int M, int S>
+__device__ __forceinline__ void level1_fixup(const float (&c)[M], float (&f)[S][M], const float (&v)[M],
+                                             const float (&Uprev)[S], const float (&Uown)[S])
+{
+#pragma unroll
+    for (int i = 0; i < M - 1; ++i)
+#pragma unroll
+        for (int s = 0; s < S; ++s) f[s][i] = fmaf(-c[i], Uown[s], fmaf(-v[i], Uprev[s], f[s][i]));
+#pragma unroll
+    for (int s = 0; s < S; ++s) f[s][M - 1] = Uown[s];
+}
+
+// ---------------------------------------------------------------------------------------------
+// level 2: one warp solves one reduced tridiagonal system of K rows held in shared memory
+// (32*M2 rows at padded index l2pad(i)).  Row k is assembled from two writers: chunk k stores
+// A, B, F and chunk k+1 stores C, Bd, Fd (its first element's share), so B+Bd and F+Fd are the
+// actual diagonal and right-hand side.  Result: the solution overwrites F[s].
+// ---------------------------------------------------------------------------------------------
+template <int S>
+__device__ void level2_solve_warp(float* A, const float* B, const float* Bd, float* C, float* F, const float* Fd,
+                                  int fstride, int M2, int lane)
+{
+    const int s0 = lane * M2, q = s0 + M2 - 1;          // interior s0..q-1, separator q
+    float xL[S], vL = -1.f, wL = 0.f;                    // last interior element (defaults: empty interior)
+    float xF[S], vF = 0.f, wF = -1.f;                    // first interior element
+#pragma unroll
+    for (int s = 0; s < S; ++s) { xL[s] = 0.f; xF[s] = 0.f; }
+    if (M2 > 1) {
+        float ct_prev = 0.f, vt_prev = 0.f, ft_prev[S];
+#pragma unroll
+        for (int s = 0; s < S; ++s) ft_prev[s] = 0.f;
+        for (int i = s0; i < q; ++i) {
+            const int p = l2pad(i);
+            const float a = A[p];
+            const float r = 1.0f / ((B[p] + Bd[p]) - a * ct_prev);
+            const float ct = C[p] * r;
+            const float vt = (i == s0) ? a * r : -(a * vt_prev) * r;
+#pragma unroll
+            for (int s = 0; s < S; ++s) { const float ft = ((F[s * fstride + p] + Fd[s * fstride + p]) - a * ft_prev[s]) * r; F[s * fstride + p] = ft; ft_prev[s] = ft; }
+            C[p] = ct; A[p] = vt; ct_prev = ct; vt_prev = vt;
+        }
+        float w_next = ct_prev, v_next = vt_prev, x_next[S];
+#pragma unroll
+        for (int s = 0; s < S; ++s) x_next[s] = ft_prev[s];
+        wL = w_next; vL = v_next;
+#pragma unroll
+        for (int s = 0; s < S; ++s) xL[s] = x_next[s];
+        for (int i = q - 2; i >= s0; --i) {
+            const int p = l2pad(i);
+            const float ct = C[p];
+#pragma unroll
+            for (int s = 0; s < S; ++s) { x_next[s] = fmaf(-ct, x_next[s], F[s * fstride + p]); F[s * fstride + p] = x_next[s]; }
+            v_next = fmaf(-ct, v_next, A[p]); A[p] = v_next;
+            w_next = -ct * w_next; C[p] = w_next;
+        }
+        vF = v_next; wF = w_next;
+#pragma unroll
+        for (int s = 0; s < S; ++s) xF[s] = x_next[s];
+    }
+    // this lane's row of the 32-row system; the next lane's first element enters through C_q
+    const int pq = l2pad(q);
+    const float Aq = A[pq], Bq = B[pq] + Bd[pq], Cq = C[pq];
+    const unsigned FULL = 0xffffffffu;
+    float nvF = __shfl_down_sync(FULL, vF, 1), nwF = __shfl_down_sync(FULL, wF, 1);
+    if (lane == 31) { nvF = 0.f; nwF = 0.f; }
+    float a = -Aq * vL;
+    float b = Bq - Aq * wL - Cq * nvF;
+    float c = -Cq * nwF;
+    float g[S];
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        float nxF = __shfl_down_sync(FULL, xF[s], 1);
+        if (lane == 31) nxF = 0.f;
+        g[s] = (F[s * fstride + pq] + Fd[s * fstride + pq]) - Aq * xL[s] - Cq * nxF;
+    }
+    // parallel cyclic reduction across the 32 lanes
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        float am = __shfl_up_sync(FULL, a, d), bm = __shfl_up_sync(FULL, b, d), cm = __shfl_up_sync(FULL, c, d);
+        float ap = __shfl_down_sync(FULL, a, d), bp = __shfl_down_sync(FULL, b, d), cp = __shfl_down_sync(FULL, c, d);
+        const bool lo = lane < d, hi = lane + d > 31;
+        if (lo) { am = 0.f; bm = 1.f; cm = 0.f; }
+        if (hi) { ap = 0.f; bp = 1.f; cp = 0.f; }
+        const float k1 = a / bm, k2 = c / bp;
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            float gm = __shfl_up_sync(FULL, g[s], d), gp = __shfl_down_sync(FULL, g[s], d);
+            if (lo) gm = 0.f;
+            if (hi) gp = 0.f;
+            g[s] = g[s] - gm * k1 - gp * k2;
+        }
+        b = b - cm * k1 - ap * k2;
+        a = -am * k1;
+        c = -cp * k2;
+    }
+    float U[S], Up[S];
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        U[s] = g[s] / b;
+        Up[s] = __shfl_up_sync(FULL, U[s], 1);
+        if (lane == 0) Up[s] = 0.f;
+    }
+    for (int i = s0; i < q; ++i) {
+        const int p = l2pad(i);
+        const float vv = A[p], ww = C[p];
+#pragma unroll
+        for (int s = 0; s < S; ++s) F[s * fstride + p] = fmaf(-ww, U[s], fmaf(-vv, Up[s], F[s * fstride + p]));
+    }
+#pragma unroll
+    for (int s = 0; s < S; ++s) F[s * fstride + pq] = U[s];
+}
+
+}  // namespace dwls

@@ -1,0 +1,139 @@
+/* dwls_b200.h — C-ABI of the B200-native disparity WLS filtering library (libdwls_b200.so).
+ *
+ * This is the drop-in boundary: the entry points below are what a binding of the reference's
+ * ximgproc disparity-filtering path would call instead of the CPU implementation.  Plain
+ * pointers, sizes and strides only (no OpenCV, no torch types).  All file:line citations are
+ * relative to the reference tree (modules/ximgproc/...).
+ *
+ *   DisparityWLSFilterImpl::filter        src/disparity_filters.cpp:219-298   -> dwls_filter_host / dwls_filter_batch_dev
+ *   DisparityWLSFilter getters            src/disparity_filters.cpp:126-139   -> conf / roi_out arguments
+ *   FastGlobalSmootherFilterImpl::init    src/fgs_filter.cpp:141-173          -> dwls_fgs_* (weights are rebuilt per call,
+ *   FastGlobalSmootherFilterImpl::filter  src/fgs_filter.cpp:182-233             LUT cached per sigma inside the ctx)
+ *   fastGlobalSmootherFilter              src/fgs_filter.cpp:687-691          -> dwls_fgs_host / dwls_fgs_dev
+ *   ComputeDiscontinuityAwareLRC_ParBody  src/disparity_filters.cpp:306-341   -> dwls_lrc_mask_host (debug / parity export)
+ *
+ * Error model: every call returns a dwls_status; nothing throws across the ABI.  The
+ * reference raises cv::Exception through CV_Assert / CV_Error (disparity_filters.cpp:221-222,
+ * 262-264; fgs_filter.cpp:143-144, 184-189); the host facades map DWLS_BAD_ARG / DWLS_BAD_SIZE
+ * back to exceptions.  There is NO CPU fallback: without a CUDA device every compute entry
+ * point fails with DWLS_CUDA_ERROR.
+ *
+ * Threading: one ctx = one CUDA device + one stream + one workspace; use one ctx per host
+ * thread (the reference's filter objects are not re-entrant either, fgs_filter.cpp:198-223).
+ */
+#ifndef DWLS_B200_H
+#define DWLS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define DWLS_API __declspec(dllexport)
+#else
+#define DWLS_API __attribute__((visibility("default")))
+#endif
+
+typedef enum dwls_status {
+    DWLS_OK = 0,
+    DWLS_BAD_ARG = 1,     /* CV_Assert on depth / channels / emptiness / parameter range */
+    DWLS_BAD_SIZE = 2,    /* CV_Error(StsBadSize) src vs guide size; ROI outside the image   */
+    DWLS_CUDA_ERROR = 3,  /* no device, launch or allocation failure                         */
+    DWLS_UNSUPPORTED = 4  /* inside the API but outside what the kernels cover (documented)  */
+} dwls_status;
+
+/* depth codes are OpenCV's: CV_8U = 0, CV_16S = 3, CV_32F = 5 */
+enum { DWLS_8U = 0, DWLS_16S = 3, DWLS_32F = 5 };
+
+/* image descriptor = the fields of a cv::Mat header the path reads */
+typedef struct dwls_image {
+    void*   data;      /* first pixel (host or device depending on the entry point) */
+    int64_t step;      /* bytes between rows (cv::Mat::step)                         */
+    int     rows, cols;
+    int     depth;     /* DWLS_8U / DWLS_16S / DWLS_32F                              */
+    int     channels;
+} dwls_image;
+
+/* DisparityWLSFilterImpl state (disparity_filters.cpp:52-63, defaults 142-159, 215) */
+typedef struct dwls_params {
+    double lambda;                /* 8000.0 */
+    double sigma_color;           /* 1.0    */
+    int    lrc_thresh;            /* 24     */
+    int    disc_radius;           /* 5      */
+    int    left_offset, right_offset, top_offset, bottom_offset;   /* matcher-derived margins, 401/407 */
+    int    use_confidence;        /* createDisparityWLSFilterGeneric(bool) */
+    double lambda_attenuation;    /* 0.25 (edge_filter.hpp:393 default)    */
+    int    num_iter;              /* 3                                      */
+} dwls_params;
+
+typedef struct dwls_ctx dwls_ctx;
+
+DWLS_API void        dwls_default_params(dwls_params* p);
+DWLS_API dwls_status dwls_ctx_create(int device, dwls_ctx** out);
+DWLS_API void        dwls_ctx_destroy(dwls_ctx* ctx);
+DWLS_API const char* dwls_last_error(const dwls_ctx* ctx);   /* ctx may be NULL: last create error */
+DWLS_API const char* dwls_version(void);
+/* number of kernels the ctx has launched so far (bench.py reports the per-step delta) */
+DWLS_API int64_t     dwls_kernel_launches(const dwls_ctx* ctx);
+/* frames processed per kernel launch group in the batch entry point (0 = choose automatically) */
+DWLS_API dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames);
+
+/* ---- DisparityWLSFilter::filter on HOST buffers (what the cv::Mat facade calls) -------------
+ * disp_left/right: CV_16SC1, same size; view: CV_8UC1/3; roi_in: user ROI {x,y,w,h} in
+ * disparity-map coordinates or NULL / zero area to derive it from the offsets (228-233).
+ * out16s: CV_16SC1 at view size, caller-allocated.  conf32f: optional CV_32FC1 at view size
+ * (getConfidenceMap, 138/274).  roi_out: the disparity-resolution ROI used (getROI, 139).
+ * Copies H2D, runs the kernels, copies D2H, synchronises. */
+DWLS_API dwls_status dwls_filter_host(dwls_ctx* ctx,
+                                      const dwls_image* disp_left, const dwls_image* disp_right,
+                                      const dwls_image* view, const int* roi_in, const dwls_params* params,
+                                      dwls_image* out16s, dwls_image* conf32f, int* roi_out);
+
+/* ---- same, on DEVICE buffers, for a batch of independent frames ------------------------------
+ * Frame f of every array starts at base + f * frame_stride (bytes).  All frames share sizes,
+ * ROI and parameters.  Asynchronous on `stream` (a cudaStream_t; NULL = the ctx stream). */
+typedef struct dwls_batch {
+    int n_frames;
+    const int16_t* disp_left;  int64_t dl_step, dl_frame;    /* bytes */
+    const int16_t* disp_right; int64_t dr_step, dr_frame;    /* NULL when !use_confidence */
+    int disp_cols, disp_rows;
+    const uint8_t* view;       int64_t view_step, view_frame;
+    int view_cols, view_rows, view_channels;
+    int16_t* out;              int64_t out_step, out_frame;   /* view size */
+    float*   conf;             int64_t conf_step, conf_frame; /* view size; NULL to skip the export */
+} dwls_batch;
+
+DWLS_API dwls_status dwls_filter_batch_dev(dwls_ctx* ctx, const dwls_batch* batch, const int* roi_in,
+                                           const dwls_params* params, int* roi_out, void* stream);
+
+/* Same batch, but every pointer of `batch` is HOST memory (pinned memory gives full PCIe speed).
+ * The library pipelines H2D copies, kernels and D2H copies over two streams and returns when the
+ * host outputs are complete. */
+DWLS_API dwls_status dwls_filter_batch_host(dwls_ctx* ctx, const dwls_batch* batch, const int* roi_in,
+                                            const dwls_params* params, int* roi_out);
+
+/* ---- fastGlobalSmootherFilter ---------------------------------------------------------------
+ * guide CV_8UC1/3; src/dst CV_8U/16S/32F with 1..4 channels, same size as guide (else
+ * DWLS_BAD_SIZE, fgs_filter.cpp:185-189). */
+DWLS_API dwls_status dwls_fgs_host(dwls_ctx* ctx, const dwls_image* guide, const dwls_image* src, dwls_image* dst,
+                                   double lambda, double sigma_color, double lambda_attenuation, int num_iter);
+DWLS_API dwls_status dwls_fgs_dev(dwls_ctx* ctx, const dwls_image* guide, const dwls_image* src, dwls_image* dst,
+                                  double lambda, double sigma_color, double lambda_attenuation, int num_iter,
+                                  void* stream);
+
+/* ---- parity / debug exports ------------------------------------------------------------------
+ * LRC decision per disparity pixel: 0 outside the ROI, 1 right index outside the right ROI
+ * (confidence kept), 2 consistent (min of both confidences), 3 inconsistent (confidence 0). */
+DWLS_API dwls_status dwls_lrc_mask_host(dwls_ctx* ctx, const dwls_image* disp_left, const dwls_image* disp_right,
+                                        int view_cols, const int* roi_in, const dwls_params* params,
+                                        uint8_t* mask, int64_t mask_step);
+/* weight planes Chor/Cvert for a host guide (fgs_filter.cpp:593-661), dense w*h floats each */
+DWLS_API dwls_status dwls_fgs_weights_host(dwls_ctx* ctx, const dwls_image* guide, double sigma_color,
+                                           float* chor, float* cvert);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DWLS_B200_H */

@@ -1,0 +1,179 @@
+"""GPU parity tests: the CUDA path (through the C-ABI) against the CPU oracle on the same inputs.
+
+Gates (BASELINE.json north_star): ROI and LRC mask bit-exact; confidence map within 1e-4
+absolute; CV_16S filtered disparity within 1 LSB on >= 99.9 % of pixels; outside-ROI fill exact.
+The envelopes of the reference's own tests are re-stated where they apply
+(test_fgs_filter.cpp:59-87, 109-151; test_disparity_wls_filter.cpp:99-153).
+"""
+import numpy as np
+import pytest
+
+import addingdisparityfiltering_b200 as A
+from addingdisparityfiltering_b200 import synth
+from oracle import oracle as O
+from tests.parity import assert_s16_parity, s16_stats
+
+pytestmark = pytest.mark.gpu
+
+
+def _guide(rng, h, w, cn):
+    g = rng.integers(0, 256, (h, w, cn)).astype(np.float32)
+    g = (g + np.roll(g, 1, 0) + np.roll(g, 1, 1)) / 3
+    g = g.astype(np.uint8)
+    return g[:, :, 0] if cn == 1 else g
+
+
+def test_lut_and_weights_match_oracle(ctx):
+    rng = np.random.default_rng(1)
+    for cn in (1, 3):
+        g = _guide(rng, 61, 127, cn)
+        for sigma in (0.5, 1.5, 10.0):
+            ch, cv = A.fgs_weights(g, sigma, ctx=ctx)
+            oh, ov = O.fgs_weights(g, sigma)
+            # LUT: float sqrt/div are IEEE on both sides; exp is correctly rounded here, <=0.502 ulp in glibc
+            for a, b in ((ch, oh), (cv, ov)):
+                rel = np.abs(a - b) / np.maximum(np.abs(b), 1e-30)
+                assert (a == b).mean() > 0.99
+                assert rel.max() < 2.5e-7
+
+
+@pytest.mark.parametrize("size", [(127, 61), (320, 240), (640, 480), (33, 9), (8, 8), (1000, 700)])
+@pytest.mark.parametrize("cn", [1, 3])
+def test_fgs_float_matches_oracle(ctx, size, cn):
+    w, h = size
+    rng = np.random.default_rng(w * 7 + h + cn)
+    g = _guide(rng, h, w, cn)
+    src = (rng.random((h, w)) * 255).astype(np.float32)
+    for lam, sigma in ((1000.0, 10.0), (8000.0, 1.5), (100.0, 50.0)):
+        got = A.fastGlobalSmootherFilter(g, src, lam, sigma, ctx=ctx)
+        ref = O.fgs_filter(g, src, lam, sigma)
+        err = np.abs(got - ref)
+        assert err.max() <= 255 * 2e-4, (lam, sigma, err.max())
+
+
+def test_fgs_constant_image_invariance(ctx):
+    # FastGlobalSmootherTest.SplatSurfaceAccuracy (test_fgs_filter.cpp:59-87): mean abs err <= 1/64
+    rng = np.random.default_rng(3)
+    for i in range(3):
+        w, h = int(rng.integers(512, 1024)), int(rng.integers(512, 1024))
+        cn = 1 if i % 2 else 3
+        g = _guide(rng, h, w, cn)
+        val = int(rng.integers(-32000, 32000))
+        src = np.full((h, w), val, np.int16)
+        out = A.fastGlobalSmootherFilter(g, src, 1000.0, 10.0, ctx=ctx)
+        assert np.abs(out.astype(np.int64) - val).mean() <= 1.0 / 64
+
+
+@pytest.mark.parametrize("dtype,cn", [(np.uint8, 1), (np.uint8, 3), (np.uint8, 4), (np.int16, 1), (np.int16, 3), (np.float32, 1), (np.float32, 2)])
+def test_fgs_type_matrix(ctx, dtype, cn):
+    # src types of FastGlobalSmootherTest.MultiThreadReproducibility (test_fgs_filter.cpp:54, 127-132)
+    rng = np.random.default_rng(11 + cn)
+    w, h = 320, 240
+    g = _guide(rng, h, w, 3)
+    shape = (h, w) if cn == 1 else (h, w, cn)
+    if dtype == np.uint8:
+        src = rng.integers(0, 256, shape).astype(np.uint8)
+    elif dtype == np.int16:
+        src = rng.integers(-32767, 32767, shape).astype(np.int16)
+    else:
+        src = ((rng.random(shape) * 2 - 1) * 1e5).astype(np.float32)
+    lam, sigma = 5000.0, 20.0
+    got = A.fastGlobalSmootherFilter(g, src, lam, sigma, ctx=ctx)
+    ref = O.fgs_filter(g, src, lam, sigma)
+    assert got.dtype == src.dtype and got.shape == src.shape
+    if dtype == np.float32:
+        assert np.abs(got - ref).max() <= 1e5 * 2e-4
+    else:
+        d = np.abs(got.astype(np.int64) - ref.astype(np.int64))
+        assert d.max() <= 1 and d.sum() <= d.size / 64          # L-inf <= 1, L1 <= total/64 (114-115)
+
+
+def _check_wls(ctx, view, dl, dr, roi, use_conf, lam=8000.0, sigma=1.5, radius=2, lrc=24):
+    f = A.createDisparityWLSFilterGeneric(use_conf, ctx=ctx)
+    f.setLambda(lam); f.setSigmaColor(sigma); f.setDepthDiscontinuityRadius(radius); f.setLRCthresh(lrc)
+    got = f.filter(dl, view, None, dr, roi)
+    ref = O.wls_filter(dl, view, dr, roi=roi, use_confidence=use_conf, lam=lam, sigma=sigma, lrc_thresh=lrc, disc_radius=radius, want_mask=True)
+    assert ref["rc"] == 0
+    assert tuple(f.getROI()) == tuple(ref["roi"])                       # ROI bit-exact
+    H, W = view.shape[:2]
+    dh, dw = dl.shape
+    sx, sy = W / np.float32(dw), H / np.float32(dh)
+    x, y, w, h = ref["roi"]
+    froi = (int(np.float32(x) * sx), int(np.float32(y) * sy), int(np.float32(w) * sx), int(np.float32(h) * sy)) if (W, H) != (dw, dh) else ref["roi"]
+    outside = np.ones((H, W), bool)
+    outside[froi[1]:froi[1] + froi[3], froi[0]:froi[0] + froi[2]] = False
+    assert (got[outside] == -16).all() and (ref["out"][outside] == -16).all()   # fill exact
+    if use_conf:
+        mask = f.lrc_mask(dl, dr, view_cols=W, ROI=roi)
+        assert (mask == ref["mask"]).all()                                # LRC decisions bit-exact
+        conf = f.getConfidenceMap()
+        assert conf.shape == (H, W)
+        assert np.abs(conf - ref["conf"]).max() <= 1e-4                   # confidence within 1e-4 absolute (0..255 scale)
+    return assert_s16_parity(got, ref["out"], froi)
+
+
+@pytest.mark.parametrize("size", [(127, 61), (320, 240), (640, 480)])
+@pytest.mark.parametrize("cn", [1, 3])
+@pytest.mark.parametrize("use_conf", [True, False])
+def test_wls_full_res_matches_oracle(ctx, size, cn, use_conf):
+    w, h = size
+    view, dl, dr, roi = synth.make_artificial_example(w, h, cn, seed=w + h + cn)
+    _check_wls(ctx, view, dl, dr, roi, use_conf, radius=5)
+    view, dl, dr = synth.make_textured_scene(w, h, cn, seed=w + cn, max_disp=max(32, w // 8))
+    md = max(32, w // 8)
+    _check_wls(ctx, view, dl, dr, (md, 0, w - md, h), use_conf, radius=2)
+
+
+@pytest.mark.parametrize("size", [(127, 61), (320, 240), (640, 480)])
+@pytest.mark.parametrize("use_conf", [True, False])
+def test_wls_half_res_matches_oracle(ctx, size, use_conf):
+    import cv2
+    w, h = size
+    view, dl, dr, roi = synth.make_artificial_example(w, h, 3, seed=5 * w + h)
+    dl2 = (cv2.resize(dl, None, fx=0.5, fy=0.5) // 2).astype(np.int16)
+    dr2 = (cv2.resize(dr, None, fx=0.5, fy=0.5) // 2).astype(np.int16)
+    roi2 = (roi[0] // 2, roi[1] // 2, roi[2] // 2, roi[3] // 2)
+    _check_wls(ctx, view, dl2, dr2, roi2, use_conf, radius=3)
+
+
+def test_wls_1080p_config2(ctx):
+    # BASELINE.json configs[1]: 1920x1080, SGBM-style geometry (ROI (160,0,1760,1080), radius 2, LRC 24)
+    view, dl, dr = synth.make_textured_scene(1920, 1080, 3, seed=42, max_disp=160)
+    st = _check_wls(ctx, view, dl, dr, (160, 0, 1760, 1080), True, lam=8000.0, sigma=1.5, radius=2)
+    print("cfg2 parity", st)
+
+
+def test_wls_matcher_factory_geometry(ctx):
+    class FakeBM:
+        kind = "bm"
+        def __init__(s): s.calls = {}
+        def getMinDisparity(s): return 0
+        def getNumDisparities(s): return 80
+        def getBlockSize(s): return 7
+        def __getattr__(s, n):
+            if n.startswith("set"):
+                return lambda v: s.calls.__setitem__(n, v)
+            raise AttributeError(n)
+    m = FakeBM()
+    f = A.createDisparityWLSFilter(m, ctx=ctx)
+    assert m.calls == {"setDisp12MaxDiff": 1000000, "setSpeckleWindowSize": 0, "setTextureThreshold": 0, "setUniquenessRatio": 0}
+    assert f.getDepthDiscontinuityRadius() == 3 and f.getLRCthresh() == 24 and f.getLambda() == 8000.0 and f.getSigmaColor() == 1.0
+    view, dl, dr, _ = synth.make_artificial_example(320, 240, 3, seed=9)
+    f.filter(dl, view, None, dr)
+    assert f.getROI() == (83, 3, 234, 234)                               # SURVEY section 8 config 1 geometry
+
+
+def test_error_behaviour(ctx):
+    view, dl, dr, roi = synth.make_artificial_example(64, 48, 3, seed=1)
+    f = A.createDisparityWLSFilterGeneric(True, ctx=ctx)
+    with pytest.raises(A.DwlsError):
+        f.filter(dl.astype(np.float32), view, None, dr, roi)             # CV_Assert depth (221)
+    with pytest.raises(A.DwlsError):
+        f.filter(dl, view, None, None, roi)                              # right map required (262)
+    with pytest.raises(A.DwlsError):
+        f.filter(dl, view, None, dr[:, :-1], roi)                        # size mismatch (263)
+    with pytest.raises(A.DwlsError) as e:
+        A.fastGlobalSmootherFilter(view, np.zeros((10, 10), np.float32), 100.0, 1.0, ctx=ctx)
+    assert e.value.status == 2                                           # StsBadSize (185-189)
+    with pytest.raises(A.DwlsError):
+        A.fastGlobalSmootherFilter(view, dl, -1.0, 1.0, ctx=ctx)         # lambda >= 0 (143)
