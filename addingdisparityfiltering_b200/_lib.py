@@ -49,7 +49,7 @@ class Batch(C.Structure):
 
 
 EXPORTS = ["dwls_default_params", "dwls_ctx_create", "dwls_ctx_destroy", "dwls_last_error", "dwls_version",
-           "dwls_kernel_launches", "dwls_set_group_frames", "dwls_filter_host", "dwls_filter_batch_dev",
+           "dwls_kernel_launches", "dwls_set_group_frames", "dwls_set_kernel_timing", "dwls_kernel_timing_report", "dwls_filter_host", "dwls_filter_batch_dev",
            "dwls_filter_batch_host", "dwls_fgs_host", "dwls_fgs_dev", "dwls_lrc_mask_host", "dwls_fgs_weights_host"]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -87,6 +87,7 @@ def lib():
             L.dwls_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
             L.dwls_ctx_destroy.argtypes = [C.c_void_p]
             L.dwls_set_group_frames.argtypes = [C.c_void_p, C.c_int]
+            L.dwls_set_kernel_timing.argtypes = [C.c_void_p, C.c_int]
             _lib = L
     return _lib
 
@@ -137,6 +138,18 @@ class Context:
 
     def set_group_frames(self, n):
         self.check(lib().dwls_set_group_frames(self._h, int(n)))
+
+    def set_kernel_timing(self, on):
+        self.check(lib().dwls_set_kernel_timing(self._h, int(bool(on))))
+
+    def kernel_timing_report(self):
+        """{kernel name: (launches, total_ms)} since the last report (synchronises the device)."""
+        cap = 32
+        names = (C.c_char_p * cap)()
+        n = (C.c_int64 * cap)()
+        ms = (C.c_double * cap)()
+        k = lib().dwls_kernel_timing_report(self._h, names, n, ms, cap)
+        return {names[i].decode(): (int(n[i]), float(ms[i])) for i in range(k)}
 
 
 _default_ctx = {}

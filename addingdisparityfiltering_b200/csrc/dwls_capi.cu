@@ -7,6 +7,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <string>
+#include <vector>
 
 #include "../../include/dwls_b200.h"
 #include "dwls_resize.cuh"
@@ -23,7 +24,35 @@ struct dwls_ctx {
     float* lut = nullptr; float lut_sigma = -1.f;           // per-sigma LUT cache (fgs_filter.cpp:150-154)
     void* ws = nullptr; size_t ws_bytes = 0;                // solver workspace (grow-only)
     void* stage = nullptr; size_t stage_bytes = 0;          // device staging of the host entry points
+    // optional per-kernel CUDA-event timing (bench.py's roofline block)
+    bool timing = false;
+    struct Span { int id; cudaEvent_t a, b; };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> free_events;
 };
+
+enum KernelId { K_LUT = 0, K_WEIGHTS, K_CONF_R, K_CONF_L, K_UPSCALE, K_PREP, K_FILL, K_HSOLVE, K_VSOLVE, K_VSOLVE_FIN, K_UNPACK, K_PACK, K_COUNT };
+static const char* const kKernelNames[K_COUNT] = { "lut_kernel", "weights_kernel", "conf_kernel<right>", "conf_kernel<left+lrc>", "upscale_prep_kernel",
+                                                   "prep_noconf_kernel", "fill_outside_kernel", "hsolve_kernel", "vsolve_kernel", "vsolve_kernel<final>",
+                                                   "unpack_kernel", "pack_kernel" };
+
+// counts the launch and, when timing is on, brackets it with CUDA events on the launching stream
+struct KTimer {
+    dwls_ctx* c; cudaStream_t st; cudaEvent_t stop = nullptr;
+    static cudaEvent_t get(dwls_ctx* c) {
+        if (!c->free_events.empty()) { cudaEvent_t e = c->free_events.back(); c->free_events.pop_back(); return e; }
+        cudaEvent_t e = nullptr; cudaEventCreate(&e); return e;
+    }
+    KTimer(dwls_ctx* ctx, int id, cudaStream_t s) : c(ctx), st(s) {
+        c->launches++;
+        if (!c->timing) return;
+        cudaEvent_t a = get(c); stop = get(c);
+        cudaEventRecord(a, st);
+        c->spans.push_back({ id, a, stop });
+    }
+    ~KTimer() { if (stop) cudaEventRecord(stop, st); }
+};
+#define TIMED(id, st, ...) do { KTimer kt_(ctx, id, st); __VA_ARGS__; } while (0)
 
 static std::string g_create_err;
 
@@ -93,6 +122,8 @@ void dwls_ctx_destroy(dwls_ctx* ctx)
     if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
     if (ctx->stream2) { cudaStreamSynchronize(ctx->stream2); cudaStreamDestroy(ctx->stream2); }
     cudaFree(ctx->lut); cudaFree(ctx->ws); cudaFree(ctx->stage);
+    for (auto& sp : ctx->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+    for (auto e : ctx->free_events) cudaEventDestroy(e);
     delete ctx;
 }
 
@@ -103,6 +134,33 @@ dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames)
     if (!ctx || frames < 0) return DWLS_BAD_ARG;
     ctx->group_frames = frames;
     return DWLS_OK;
+}
+
+dwls_status dwls_set_kernel_timing(dwls_ctx* ctx, int on)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    ctx->timing = on != 0;
+    return DWLS_OK;
+}
+
+// synchronises the ctx streams, folds the recorded spans into per-kernel totals and clears them.
+// names[i] / launches[i] / total_ms[i] for i < returned count (<= cap)
+int dwls_kernel_timing_report(dwls_ctx* ctx, const char** names, int64_t* launches, double* total_ms, int cap)
+{
+    if (!ctx) return 0;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    int64_t n[K_COUNT] = { 0 }; double ms[K_COUNT] = { 0 };
+    for (auto& sp : ctx->spans) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, sp.a, sp.b) == cudaSuccess) { n[sp.id]++; ms[sp.id] += t; }
+        ctx->free_events.push_back(sp.a); ctx->free_events.push_back(sp.b);
+    }
+    ctx->spans.clear();
+    int k = 0;
+    for (int i = 0; i < K_COUNT && k < cap; ++i)
+        if (n[i]) { names[k] = kKernelNames[i]; launches[k] = n[i]; total_ms[k] = ms[i]; ++k; }
+    return k;
 }
 
 }  // extern "C"
@@ -116,9 +174,8 @@ static dwls_status ensure_lut(dwls_ctx* ctx, float sigma, cudaStream_t st)
 {
     if (!ctx->lut) CK(cudaMalloc(&ctx->lut, sizeof(float) * LUT_LEVELS));
     if (ctx->lut_sigma != sigma) {
-        lut_kernel<<<(LUT_LEVELS + 255) / 256, 256, 0, st>>>(ctx->lut, LUT_LEVELS, sigma);
+        TIMED(K_LUT, st, lut_kernel<<<(LUT_LEVELS + 255) / 256, 256, 0, st>>>(ctx->lut, LUT_LEVELS, sigma));
         CK(cudaGetLastError());
-        ctx->launches++;
         ctx->lut_sigma = sigma;
     }
     return DWLS_OK;
@@ -142,11 +199,11 @@ template <int S>
 static dwls_status launch_h(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
     const size_t smem = sizeof(float) * (4 + 2 * S) * l2pad_size(pl.hK);
+    KTimer kt_(ctx, K_HSOLVE, st);
     if (pl.hK <= 256) hsolve_kernel<S, 256><<<dim3(a.h, frames), pl.hK, smem, st>>>(a);
     else if (pl.hK <= 512) hsolve_kernel<S, 512><<<dim3(a.h, frames), pl.hK, smem, st>>>(a);
     else hsolve_kernel<S, 1024><<<dim3(a.h, frames), pl.hK, smem, st>>>(a);
     CK(cudaGetLastError());
-    ctx->launches++;
     return DWLS_OK;
 }
 
@@ -156,9 +213,8 @@ static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
     const size_t smem = sizeof(float) * COLS * (4 + 2 * S) * l2pad_size(pl.vK);
     auto k = vsolve_kernel<M, S, COLS, FIN, MAXT>;
     if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<dim3((a.w + COLS - 1) / COLS, frames), COLS * pl.vK, smem, st>>>(a);
+    TIMED(FIN == FIN_FLOAT ? K_VSOLVE : K_VSOLVE_FIN, st, k<<<dim3((a.w + COLS - 1) / COLS, frames), COLS * pl.vK, smem, st>>>(a));
     CK(cudaGetLastError());
-    ctx->launches++;
     return DWLS_OK;
 }
 
@@ -197,10 +253,10 @@ static dwls_status launch_weights(dwls_ctx* ctx, const uint8_t* guide, int64_t g
                                   int pitch, float* chor, float* cvert, int64_t wframe, int frames, cudaStream_t st)
 {
     dim3 grid((pitch + 255) / 256, h, frames);
+    KTimer kt_(ctx, K_WEIGHTS, st);
     if (cn == 1) weights_kernel<1><<<grid, 256, 0, st>>>(guide, gstep, gframe, w, h, pitch, ctx->lut, chor, cvert, wframe);
     else weights_kernel<3><<<grid, 256, 0, st>>>(guide, gstep, gframe, w, h, pitch, ctx->lut, chor, cvert, wframe);
     CK(cudaGetLastError());
-    ctx->launches++;
     return DWLS_OK;
 }
 
@@ -296,11 +352,10 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
         a.p_frame = L.plane; a.pitch = g.pitch;
         a.mask = mask; a.mask_step = mask_step;
         const size_t smem = sizeof(int16_t) * (CT_W + 2 * a.radius) * (CT_H + 2 * a.radius);
-        conf_kernel<false><<<dim3((g.rw + CT_W - 1) / CT_W, (g.rh + CT_H - 1) / CT_H, nf), dim3(CT_W, CT_H), smem, st>>>(a);
+        TIMED(K_CONF_R, st, conf_kernel<false><<<dim3((g.rw + CT_W - 1) / CT_W, (g.rh + CT_H - 1) / CT_H, nf), dim3(CT_W, CT_H), smem, st>>>(a));
         CK(cudaGetLastError());
-        conf_kernel<true><<<dim3((g.dw + CT_W - 1) / CT_W, (g.dh + CT_H - 1) / CT_H, nf), dim3(CT_W, CT_H), smem, st>>>(a);
+        TIMED(K_CONF_L, st, conf_kernel<true><<<dim3((g.dw + CT_W - 1) / CT_W, (g.dh + CT_H - 1) / CT_H, nf), dim3(CT_W, CT_H), smem, st>>>(a));
         CK(cudaGetLastError());
-        ctx->launches += 2;
         if (mask_only) return DWLS_OK;
     }
     if (!g.same) {
@@ -314,18 +369,15 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
         u.fx = g.fx; u.fy = g.fy; u.fw = g.fw; u.fh = g.fh;
         u.conf = conf ? cexp : nullptr; u.conf_step = b->conf_step / 4; u.conf_frame = b->conf_frame / 4;
         u.plane_dc = p0; u.plane_c = conf ? p1 : nullptr; u.p_frame = L.plane; u.pitch = g.pitch;
-        upscale_prep_kernel<<<dim3((g.W + 255) / 256, g.H, nf), 256, 0, st>>>(u);
+        TIMED(K_UPSCALE, st, upscale_prep_kernel<<<dim3((g.W + 255) / 256, g.H, nf), 256, 0, st>>>(u));
         CK(cudaGetLastError());
-        ctx->launches++;
     } else if (!conf) {
-        prep_noconf_kernel<<<dim3((g.fw + 255) / 256, g.fh, nf), 256, 0, st>>>(dl + (size_t)g.fy * (b->dl_step / 2) + g.fx, b->dl_step / 2,
-                                                                            b->dl_frame / 2, g.fw, g.fh, p0, L.plane, g.pitch);
+        TIMED(K_PREP, st, prep_noconf_kernel<<<dim3((g.fw + 255) / 256, g.fh, nf), 256, 0, st>>>(dl + (size_t)g.fy * (b->dl_step / 2) + g.fx, b->dl_step / 2,
+                                                                            b->dl_frame / 2, g.fw, g.fh, p0, L.plane, g.pitch));
         CK(cudaGetLastError());
-        ctx->launches++;
     }
-    fill_outside_kernel<<<dim3((g.W + 255) / 256, g.H, nf), 256, 0, st>>>(out, b->out_step / 2, b->out_frame / 2, g.W, g.H, g.fx, g.fy, g.fw, g.fh);
+    TIMED(K_FILL, st, fill_outside_kernel<<<dim3((g.W + 255) / 256, g.H, nf), 256, 0, st>>>(out, b->out_step / 2, b->out_frame / 2, g.W, g.H, g.fx, g.fy, g.fw, g.fh));
     CK(cudaGetLastError());
-    ctx->launches++;
     dwls_status s = launch_weights(ctx, view + (size_t)g.fy * b->view_step + (size_t)g.fx * g.vcn, b->view_step, b->view_frame, g.vcn,
                                    g.fw, g.fh, g.pitch, chor, cvert, L.plane, nf, st);
     if (s) return s;
@@ -526,11 +578,11 @@ static dwls_status fgs_dev_impl(dwls_ctx* ctx, const dwls_image* guide, const dw
         CK(cudaMemcpy2DAsync(cvert_out, (size_t)w * 4, cvert, (size_t)pitch * 4, (size_t)w * 4, h, cudaMemcpyDeviceToDevice, st));
         return DWLS_OK;
     }
+    { KTimer kt_(ctx, K_UNPACK, st);
     if (src->depth == DWLS_8U) launch_unpack<uint8_t>(src, planes, plane, pitch, st);
     else if (src->depth == DWLS_16S) launch_unpack<int16_t>(src, planes, plane, pitch, st);
-    else launch_unpack<float>(src, planes, plane, pitch, st);
+    else launch_unpack<float>(src, planes, plane, pitch, st); }
     CK(cudaGetLastError());
-    ctx->launches++;
     // channels are independent solves sharing the weights (fgs_filter.cpp:200-221): two planes per launch
     for (int c0 = 0; c0 < S; c0 += 2) {
         const int ns = (S - c0 >= 2) ? 2 : 1;
@@ -540,11 +592,11 @@ static dwls_status fgs_dev_impl(dwls_ctx* ctx, const dwls_image* guide, const dw
         for (int k = 0; k < ns; ++k) { a.in[k] = planes + (size_t)(c0 + k) * plane; a.out[k] = planes + (size_t)(c0 + k) * plane; }
         if ((s = run_sweeps(ctx, a, chor, cvert, ns, FIN_FLOAT, pl, 1, lambda, att, num_iter, st))) return s;
     }
+    { KTimer kt_(ctx, K_PACK, st);
     if (dst->depth == DWLS_8U) launch_pack<uint8_t>(planes, plane, pitch, dst, st);
     else if (dst->depth == DWLS_16S) launch_pack<int16_t>(planes, plane, pitch, dst, st);
-    else launch_pack<float>(planes, plane, pitch, dst, st);
+    else launch_pack<float>(planes, plane, pitch, dst, st); }
     CK(cudaGetLastError());
-    ctx->launches++;
     return DWLS_OK;
 }
 

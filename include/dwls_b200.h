@@ -77,6 +77,10 @@ DWLS_API const char* dwls_last_error(const dwls_ctx* ctx);   /* ctx may be NULL:
 DWLS_API const char* dwls_version(void);
 /* number of kernels the ctx has launched so far (bench.py reports the per-step delta) */
 DWLS_API int64_t     dwls_kernel_launches(const dwls_ctx* ctx);
+/* per-kernel CUDA-event timing on the launching stream (off by default).  The report synchronises
+ * the device, returns one entry per kernel that ran since the last report and resets the record. */
+DWLS_API dwls_status dwls_set_kernel_timing(dwls_ctx* ctx, int on);
+DWLS_API int         dwls_kernel_timing_report(dwls_ctx* ctx, const char** names, int64_t* launches, double* total_ms, int cap);
 /* frames processed per kernel launch group in the batch entry point (0 = choose automatically) */
 DWLS_API dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames);
 
