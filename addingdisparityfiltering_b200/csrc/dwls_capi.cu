@@ -33,7 +33,7 @@ struct dwls_ctx {
 
 enum KernelId { K_LUT = 0, K_WEIGHTS, K_CONF_R, K_CONF_L, K_UPSCALE, K_PREP, K_FILL, K_HSOLVE, K_VSOLVE, K_VSOLVE_FIN, K_UNPACK, K_PACK, K_COUNT };
 static const char* const kKernelNames[K_COUNT] = { "lut_kernel", "weights_kernel", "conf_kernel<right>", "conf_kernel<left+lrc>", "upscale_prep_kernel",
-                                                   "prep_noconf_kernel", "fill_outside_kernel", "hsolve_kernel", "vsolve_kernel", "vsolve_kernel<final>",
+                                                   "prep_noconf_kernel", "border_kernel", "hsolve_kernel", "vsolve_kernel", "vsolve_kernel<final>",
                                                    "unpack_kernel", "pack_kernel" };
 
 // counts the launch and, when timing is on, brackets it with CUDA events on the launching stream
@@ -260,6 +260,19 @@ static dwls_status launch_weights(dwls_ctx* ctx, const uint8_t* guide, int64_t g
     return DWLS_OK;
 }
 
+static dwls_status launch_border(dwls_ctx* ctx, const BorderArgs& ba, int frames, cudaStream_t st)
+{
+    if (ba.W > ba.rw) {
+        TIMED(K_FILL, st, border_kernel<true><<<dim3((ba.W - ba.rw + 255) / 256, ba.rh, frames), 256, 0, st>>>(ba));
+        CK(cudaGetLastError());
+    }
+    if (ba.H > ba.rh) {
+        TIMED(K_FILL, st, border_kernel<false><<<dim3((ba.W + 255) / 256, ba.H - ba.rh, frames), 256, 0, st>>>(ba));
+        CK(cudaGetLastError());
+    }
+    return DWLS_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // DisparityWLSFilter::filter on device buffers
 // ---------------------------------------------------------------------------------------------
@@ -301,7 +314,7 @@ static dwls_status check_params(dwls_ctx* ctx, const dwls_params* p)
     if (!p) return fail(ctx, DWLS_BAD_ARG, "params is NULL");
     if (!(p->lambda >= 0) || !(p->sigma_color >= 0) || p->num_iter < 1)                       // fgs_filter.cpp:143
         return fail(ctx, DWLS_BAD_ARG, "lambda >= 0, sigma_color >= 0 and num_iter >= 1 are required");
-    if (p->use_confidence && (p->disc_radius < 0 || p->disc_radius > 32)) return fail(ctx, DWLS_UNSUPPORTED, "depth discontinuity radius must be in [0, 32]");
+    if (p->use_confidence && (p->disc_radius < 0 || p->disc_radius > 64)) return fail(ctx, DWLS_UNSUPPORTED, "depth discontinuity radius must be in [0, 64]");
     return DWLS_OK;
 }
 
@@ -351,11 +364,20 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
         if (mask_only) { a.conf = nullptr; a.plane_dc = nullptr; a.plane_c = nullptr; }
         a.p_frame = L.plane; a.pitch = g.pitch;
         a.mask = mask; a.mask_step = mask_step;
-        const size_t smem = sizeof(int16_t) * (CT_W + 2 * a.radius) * (CT_H + 2 * a.radius);
-        TIMED(K_CONF_R, st, conf_kernel<false><<<dim3((g.rw + CT_W - 1) / CT_W, (g.rh + CT_H - 1) / CT_H, nf), dim3(CT_W, CT_H), smem, st>>>(a));
+        const int tw = CF_T - 2 * a.radius;
+        const dim3 cgrid((g.rw + tw - 1) / tw, (g.rh + CF_ROWS - 1) / CF_ROWS, nf);
+        TIMED(K_CONF_R, st, conf_kernel<false><<<cgrid, CF_T, 0, st>>>(a));
         CK(cudaGetLastError());
-        TIMED(K_CONF_L, st, conf_kernel<true><<<dim3((g.dw + CT_W - 1) / CT_W, (g.dh + CT_H - 1) / CT_H, nf), dim3(CT_W, CT_H), smem, st>>>(a));
+        TIMED(K_CONF_L, st, conf_kernel<true><<<cgrid, CF_T, 0, st>>>(a));
         CK(cudaGetLastError());
+        if (a.conf || a.mask) {          // zero the exported map (and the mask) outside the ROI (disparity_filters.cpp:187)
+            BorderArgs ba;
+            memset(&ba, 0, sizeof ba);
+            ba.conf = a.conf; ba.conf_step = a.conf_step; ba.conf_frame = a.conf_frame; ba.mask = a.mask; ba.mask_step = a.mask_step;
+            ba.W = g.dw; ba.H = g.dh; ba.rx = g.rx; ba.ry = g.ry; ba.rw = g.rw; ba.rh = g.rh;
+            dwls_status bs = launch_border(ctx, ba, nf, st);
+            if (bs) return bs;
+        }
         if (mask_only) return DWLS_OK;
     }
     if (!g.same) {
@@ -376,8 +398,14 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
                                                                             b->dl_frame / 2, g.fw, g.fh, p0, L.plane, g.pitch));
         CK(cudaGetLastError());
     }
-    TIMED(K_FILL, st, fill_outside_kernel<<<dim3((g.W + 255) / 256, g.H, nf), 256, 0, st>>>(out, b->out_step / 2, b->out_frame / 2, g.W, g.H, g.fx, g.fy, g.fw, g.fh));
-    CK(cudaGetLastError());
+    {
+        BorderArgs ba;
+        memset(&ba, 0, sizeof ba);
+        ba.out = out; ba.out_step = b->out_step / 2; ba.out_frame = b->out_frame / 2;
+        ba.W = g.W; ba.H = g.H; ba.rx = g.fx; ba.ry = g.fy; ba.rw = g.fw; ba.rh = g.fh;
+        dwls_status bs = launch_border(ctx, ba, nf, st);
+        if (bs) return bs;
+    }
     dwls_status s = launch_weights(ctx, view + (size_t)g.fy * b->view_step + (size_t)g.fx * g.vcn, b->view_step, b->view_frame, g.vcn,
                                    g.fw, g.fh, g.pitch, chor, cvert, L.plane, nf, st);
     if (s) return s;

@@ -109,13 +109,13 @@ __device__ __forceinline__ void level1_fixup(const float (&c)[M], float (&f)[S][
 }
 
 // ---------------------------------------------------------------------------------------------
-// level 2: one warp solves one reduced tridiagonal system of K rows held in shared memory
+// level 2, generic trip count (wide rows only, M2 > 8): chunks stay in shared memory
 // (32*M2 rows at padded index l2pad(i)).  Row k is assembled from two writers: chunk k stores
 // A, B, F and chunk k+1 stores C, Bd, Fd (its first element's share), so B+Bd and F+Fd are the
 // actual diagonal and right-hand side.  Result: the solution overwrites F[s].
 // ---------------------------------------------------------------------------------------------
 template <int S>
-__device__ void level2_solve_warp(float* A, const float* B, const float* Bd, float* C, float* F, const float* Fd,
+__device__ __noinline__ void level2_solve_loop(float* A, const float* B, const float* Bd, float* C, float* F, const float* Fd,
                                   int fstride, int M2, int lane)
 {
     const int s0 = lane * M2, q = s0 + M2 - 1;          // interior s0..q-1, separator q
@@ -206,6 +206,125 @@ __device__ void level2_solve_warp(float* A, const float* B, const float* Bd, flo
     }
 #pragma unroll
     for (int s = 0; s < S; ++s) F[s * fstride + pq] = U[s];
+}
+
+// ---------------------------------------------------------------------------------------------
+// level 2: one warp solves one reduced tridiagonal system of 32*M2 rows held in shared memory at
+// padded index l2pad(i).  Row k is assembled from two writers: chunk k stores A, B, F and chunk
+// k+1 stores C, Bd, Fd (its first element's share), so B+Bd and F+Fd are the actual diagonal and
+// right-hand side.  Each lane pulls its M2 consecutive rows into registers, eliminates its M2-1
+// interior rows (same step as level 1), the 32 separator rows are solved by parallel cyclic
+// reduction over warp shuffles, and the solution overwrites F[s].
+// This is the only serial section of a sweep (the other warps of the CTA wait at a barrier), so
+// it is written for latency: all loads issued up front, compile-time trip counts, reciprocals
+// by MUFU + one Newton step (every pivot is >= 1: the Schur complements stay diagonally dominant).
+// ---------------------------------------------------------------------------------------------
+template <int S, int M2>
+__device__ __forceinline__ void level2_solve_regs(float* A, const float* B, const float* Bd, float* C, float* F, const float* Fd,
+                                                  int fstride, int lane)
+{
+    const unsigned FULL = 0xffffffffu;
+    const int s0 = lane * M2;
+    float a[M2], b[M2], c[M2], f[S][M2];
+#pragma unroll
+    for (int i = 0; i < M2; ++i) {
+        const int p = l2pad(s0 + i);
+        a[i] = A[p]; b[i] = B[p] + Bd[p]; c[i] = C[p];
+#pragma unroll
+        for (int s = 0; s < S; ++s) f[s][i] = F[s * fstride + p] + Fd[s * fstride + p];
+    }
+    // interior rows 0..M2-2: forward elimination with the left spike in a[], then back substitution
+    // leaving u_i = f[s][i] - a[i]*U_prev - c[i]*U_own
+    float xL[S], vL = -1.f, wL = 0.f, xF[S], vF = 0.f, wF = -1.f;     // defaults describe an empty interior (M2 == 1)
+#pragma unroll
+    for (int s = 0; s < S; ++s) { xL[s] = 0.f; xF[s] = 0.f; }
+    if (M2 > 1) {
+#pragma unroll
+        for (int i = 0; i < M2 - 1; ++i) {
+            const float ai = a[i];
+            const float den = (i == 0) ? b[0] : fmaf(-ai, c[i - 1], b[i]);
+            const float r = rcp_nr(den);
+            c[i] = c[i] * r;
+            a[i] = (i == 0) ? ai * r : -(ai * a[i - 1]) * r;
+#pragma unroll
+            for (int s = 0; s < S; ++s) f[s][i] = ((i == 0) ? f[s][0] : fmaf(-ai, f[s][i - 1], f[s][i])) * r;
+        }
+        vL = a[M2 - 2]; wL = c[M2 - 2];
+#pragma unroll
+        for (int s = 0; s < S; ++s) xL[s] = f[s][M2 - 2];
+#pragma unroll
+        for (int i = M2 - 3; i >= 0; --i) {
+            const float ct = c[i];
+#pragma unroll
+            for (int s = 0; s < S; ++s) f[s][i] = fmaf(-ct, f[s][i + 1], f[s][i]);
+            a[i] = fmaf(-ct, a[i + 1], a[i]);
+            c[i] = -ct * c[i + 1];
+        }
+        vF = a[0]; wF = c[0];
+#pragma unroll
+        for (int s = 0; s < S; ++s) xF[s] = f[s][0];
+    }
+    // this lane's row of the 32-row system; the next lane's first interior row enters through cq
+    const float aq = a[M2 - 1], bq = b[M2 - 1], cq = c[M2 - 1];
+    float nvF = __shfl_down_sync(FULL, vF, 1), nwF = __shfl_down_sync(FULL, wF, 1);
+    if (lane == 31) { nvF = 0.f; nwF = 0.f; }
+    float pa = -aq * vL;
+    float pb = bq - aq * wL - cq * nvF;
+    float pc = -cq * nwF;
+    float g[S];
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        float nxF = __shfl_down_sync(FULL, xF[s], 1);
+        if (lane == 31) nxF = 0.f;
+        g[s] = f[s][M2 - 1] - aq * xL[s] - cq * nxF;
+    }
+    // parallel cyclic reduction across the 32 lanes (rows beyond either end act as identity rows)
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        float am = __shfl_up_sync(FULL, pa, d), bm = __shfl_up_sync(FULL, pb, d), cm = __shfl_up_sync(FULL, pc, d);
+        float ap = __shfl_down_sync(FULL, pa, d), bp = __shfl_down_sync(FULL, pb, d), cp = __shfl_down_sync(FULL, pc, d);
+        const bool lo = lane < d, hi = lane + d > 31;
+        if (lo) { am = 0.f; bm = 1.f; cm = 0.f; }
+        if (hi) { ap = 0.f; bp = 1.f; cp = 0.f; }
+        const float k1 = pa * rcp_nr(bm), k2 = pc * rcp_nr(bp);
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            float gm = __shfl_up_sync(FULL, g[s], d), gp = __shfl_down_sync(FULL, g[s], d);
+            if (lo) gm = 0.f;
+            if (hi) gp = 0.f;
+            g[s] = fmaf(-gp, k2, fmaf(-gm, k1, g[s]));
+        }
+        pb = fmaf(-ap, k2, fmaf(-cm, k1, pb));
+        pa = -am * k1;
+        pc = -cp * k2;
+    }
+    const float rb = rcp_nr(pb);
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        const float U = g[s] * rb;
+        float Up = __shfl_up_sync(FULL, U, 1);
+        if (lane == 0) Up = 0.f;
+#pragma unroll
+        for (int i = 0; i < M2 - 1; ++i) F[s * fstride + l2pad(s0 + i)] = fmaf(-c[i], U, fmaf(-a[i], Up, f[s][i]));
+        F[s * fstride + l2pad(s0 + M2 - 1)] = U;
+    }
+}
+
+template <int S>
+__device__ __forceinline__ void level2_solve_warp(float* A, const float* B, const float* Bd, float* C, float* F, const float* Fd,
+                                                  int fstride, int M2, int lane)
+{
+    switch (M2) {
+    case 1: level2_solve_regs<S, 1>(A, B, Bd, C, F, Fd, fstride, lane); break;
+    case 2: level2_solve_regs<S, 2>(A, B, Bd, C, F, Fd, fstride, lane); break;
+    case 3: level2_solve_regs<S, 3>(A, B, Bd, C, F, Fd, fstride, lane); break;
+    case 4: level2_solve_regs<S, 4>(A, B, Bd, C, F, Fd, fstride, lane); break;
+    case 5: level2_solve_regs<S, 5>(A, B, Bd, C, F, Fd, fstride, lane); break;
+    case 6: level2_solve_regs<S, 6>(A, B, Bd, C, F, Fd, fstride, lane); break;
+    case 7: level2_solve_regs<S, 7>(A, B, Bd, C, F, Fd, fstride, lane); break;
+    case 8: level2_solve_regs<S, 8>(A, B, Bd, C, F, Fd, fstride, lane); break;
+    default: level2_solve_loop<S>(A, B, Bd, C, F, Fd, fstride, M2, lane); break;
+    }
 }
 
 }  // namespace dwls

@@ -75,85 +75,112 @@ __device__ __forceinline__ int reflect101(int p, int len)
     return p;
 }
 
-constexpr int CT_W = 32, CT_H = 16;     // output tile of the confidence kernels
+constexpr int CF_T = 256;       // threads per CTA = tile columns including the 2*radius halo
+constexpr int CF_ROWS = 32;     // output rows per CTA
+constexpr int CF_PF = 4;        // rows fetched ahead per thread
 
-// discontinuity confidence of one view's ROI crop: max(1 - roll_off * (E[d^2] - E[d]^2), 0) with
-// the exact rounding sequence of boxFilter / sqrBoxFilter / ComputeDepthDisc_ParBody:
-// int window sum * float(1/k^2); exact sum of squares * double(1/k^2) -> float; unfused float ops.
-__device__ __forceinline__ float disc_conf(const int16_t* tile, int tw, int lx, int ly, int r, const ConfArgs& a)
-{
-    int s = 0; long long q = 0;
-    for (int dy = 0; dy <= 2 * r; ++dy) {
-        const int16_t* t = tile + (ly + dy) * tw + lx;
-        int rs = 0;                      // squares go straight into the 64-bit accumulator (a row of them can exceed 2^32)
-        for (int dx = 0; dx <= 2 * r; ++dx) {
-            const int v = t[dx];
-            rs += v;
-            q += (long long)(v * v);
-        }
-        s += rs;
-    }
-    const float mean = __fmul_rn((float)s, a.scale_f);
-    const float meansq = (float)__dmul_rn((double)q, a.scale_d);
-    const float variance = __fsub_rn(meansq, __fmul_rn(mean, mean));
-    return fmaxf(__fsub_rn(1.0f, __fmul_rn(a.roll_off, variance)), 0.0f);
-}
-
-// grid = (ceil(dw/CT_W), ceil(dh/CT_H), frames), block = (CT_W, CT_H); dynamic smem = tile
+// Box variance by running sums, exact in integers: every thread owns one column of the ROI crop
+// (border = reflect-101 of the CROP, disparity_filters.cpp:168-174) and slides a (2r+1)-row window
+// down it (column sum, column sum of squares); the per-row column sums go through a double-buffered
+// shared row and each output thread adds its 2r+1 neighbours.  Then the exact rounding sequence of
+// boxFilter / sqrBoxFilter / ComputeDepthDisc_ParBody (349-373): int window sum * float(1/k^2);
+// exact sum of squares * double(1/k^2) -> float; unfused float ops.
+// grid = (ceil(rw / (CF_T - 2r)), ceil(rh / CF_ROWS), frames)
 // LEFT = false: right view, writes conf_r over the right ROI.
-// LEFT = true : left view + LRC + *255 + export + planes.  Covers the whole disparity map so the
-//               exported confidence is zero outside the ROI (187).
+// LEFT = true : left view + LRC (306-341) + *255 (209) + export + solver planes (286-290).
 template <bool LEFT>
-__global__ void __launch_bounds__(CT_W * CT_H) conf_kernel(const ConfArgs a)
+__global__ void __launch_bounds__(CF_T) conf_kernel(const ConfArgs a)
 {
-    extern __shared__ int16_t tile[];
-    const int r = a.radius, tw = CT_W + 2 * r, th = CT_H + 2 * r;
-    const int frame = blockIdx.z;
-    const int x0 = blockIdx.x * CT_W, y0 = blockIdx.y * CT_H;          // full-map coordinates (LEFT) / crop coordinates (!LEFT)
+    __shared__ int cs_buf[2][CF_T];
+    __shared__ long long cq_buf[2][CF_T];
+    const int r = a.radius, tid = threadIdx.x, frame = blockIdx.z;
+    const int tw = CF_T - 2 * r;
+    const int cx = blockIdx.x * tw + tid - r;                      // crop column (halo threads fall outside [0, rw))
+    const int y0 = blockIdx.y * CF_ROWS, y1 = min(y0 + CF_ROWS, a.rh);
     const int16_t* src = LEFT ? a.dl + (size_t)frame * a.dl_frame : a.dr + (size_t)frame * a.dr_frame;
     const int64_t sstep = LEFT ? a.dl_step : a.dr_step;
-    const int ox = LEFT ? a.rx : a.rrx;                                  // crop origin in the source map
-    // tile origin in crop coordinates
-    const int cx0 = LEFT ? x0 - a.rx : x0, cy0 = LEFT ? y0 - a.ry : y0;
-    const bool tile_hits_roi = cx0 < a.rw && cx0 + CT_W > 0 && cy0 < a.rh && cy0 + CT_H > 0;
-    if (tile_hits_roi) {
-        for (int idx = threadIdx.y * CT_W + threadIdx.x; idx < tw * th; idx += CT_W * CT_H) {
-            const int ty = idx / tw, tx = idx - ty * tw;
-            const int cx = reflect101(cx0 + tx - r, a.rw), cy = reflect101(cy0 + ty - r, a.rh);   // border of the CROP (168-174)
-            tile[idx] = src[(size_t)(a.ry + cy) * sstep + ox + cx];
+    const int16_t* col = src + (size_t)a.ry * sstep + (LEFT ? a.rx : a.rrx) + reflect101(cx, a.rw);
+    const bool is_out = tid >= r && tid < CF_T - r && cx < a.rw;
+
+    int cs = 0; long long cq = 0;
+    for (int d = -r; d < r; ++d) { const int v = col[(size_t)reflect101(y0 + d, a.rh) * sstep]; cs += v; cq += v * v; }
+    for (int yb = y0; yb < y1; yb += CF_PF) {
+        int vin[CF_PF], vout[CF_PF];
+#pragma unroll
+        for (int i = 0; i < CF_PF; ++i) {
+            vin[i] = col[(size_t)reflect101(yb + i + r, a.rh) * sstep];
+            vout[i] = col[(size_t)reflect101(yb + i - r, a.rh) * sstep];
+        }
+#pragma unroll
+        for (int i = 0; i < CF_PF; ++i) {
+            const int y = yb + i;
+            if (y >= y1) break;                                     // uniform across the CTA
+            cs += vin[i]; cq += vin[i] * vin[i];
+            const int buf = i & 1;                                  // CF_PF is even, so this alternates across chunks too
+            cs_buf[buf][tid] = cs; cq_buf[buf][tid] = cq;
+            __syncthreads();
+            if (is_out) {
+                int s = 0; long long q = 0;
+                for (int d = -r; d <= r; ++d) { s += cs_buf[buf][tid + d]; q += cq_buf[buf][tid + d]; }
+                const float mean = __fmul_rn((float)s, a.scale_f);
+                const float meansq = (float)__dmul_rn((double)q, a.scale_d);
+                const float variance = __fsub_rn(meansq, __fmul_rn(mean, mean));
+                float cval = fmaxf(__fsub_rn(1.0f, __fmul_rn(a.roll_off, variance)), 0.0f);
+                if (!LEFT) {
+                    a.conf_r[(size_t)frame * a.cr_frame + (size_t)y * a.cr_pitch + cx] = cval;
+                } else {
+                    const int gx = a.rx + cx, gy = a.ry + y;
+                    const int L = col[(size_t)y * sstep];
+                    const int ridx = gx - (L >> 4);                                                   // 331
+                    uint8_t m = 1;
+                    if (ridx >= a.rrx && ridx < a.rrx + a.rw) {                                        // 332
+                        const int R = a.dr[(size_t)frame * a.dr_frame + (size_t)gy * a.dr_step + ridx];
+                        if (abs(L + R) < a.thresh) {                                                   // 334
+                            cval = fminf(cval, a.conf_r[(size_t)frame * a.cr_frame + (size_t)y * a.cr_pitch + (ridx - a.rrx)]);
+                            m = 2;
+                        } else { cval = 0.0f; m = 3; }
+                    }
+                    cval = __fmul_rn(255.0f, cval);                                                    // 209
+                    if (a.mask && frame == 0) a.mask[(size_t)gy * a.mask_step + gx] = m;
+                    if (a.plane_c) {
+                        const size_t po = (size_t)frame * a.p_frame + (size_t)y * a.pitch + cx;
+                        a.plane_c[po] = cval;
+                        a.plane_dc[po] = __fmul_rn(cval, (float)L);                                    // 289-290
+                    }
+                    if (a.conf) a.conf[(size_t)frame * a.conf_frame + (size_t)gy * a.conf_step + gx] = cval;
+                }
+            }
+            cs -= vout[i]; cq -= vout[i] * vout[i];
         }
     }
-    __syncthreads();
-    const int cx = cx0 + threadIdx.x, cy = cy0 + threadIdx.y;
-    const bool in_roi = cx >= 0 && cx < a.rw && cy >= 0 && cy < a.rh;
-    if (!LEFT) {
-        if (in_roi) a.conf_r[(size_t)frame * a.cr_frame + (size_t)cy * a.cr_pitch + cx] = disc_conf(tile, tw, threadIdx.x, threadIdx.y, r, a);
-        return;
+}
+
+// everything outside the ROI: filtered output = 16*(min_disp-1) with min_disp forced to 0
+// (disparity_filters.cpp:149,254,284) and, when exported, confidence = 0 (187) / mask = 0.
+// Two launches cover only the border: side bands (rows of the ROI, columns outside it) and the
+// top/bottom bands (full rows).  grid = (ceil(cols/256), rows, frames)
+struct BorderArgs {
+    int16_t* out; int64_t out_step, out_frame;       // elements; may be NULL
+    float* conf; int64_t conf_step, conf_frame;      // elements; may be NULL
+    uint8_t* mask; int64_t mask_step;                // may be NULL (frame 0 only)
+    int W, H, rx, ry, rw, rh;
+};
+template <bool SIDES>
+__global__ void __launch_bounds__(256) border_kernel(const BorderArgs a)
+{
+    int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    const int frame = blockIdx.z;
+    if (SIDES) {
+        if (j >= a.W - a.rw) return;
+        if (j >= a.rx) j += a.rw;
+        i += a.ry;
+    } else {
+        if (j >= a.W) return;
+        if (i >= a.ry) i += a.rh;
     }
-    const int gx = x0 + threadIdx.x, gy = y0 + threadIdx.y;
-    if (gx >= a.dw || gy >= a.dh) return;
-    float cval = 0.f;
-    if (in_roi) {
-        cval = disc_conf(tile, tw, threadIdx.x, threadIdx.y, r, a);
-        const int L = tile[(threadIdx.y + r) * tw + threadIdx.x + r];
-        const int ridx = gx - (L >> 4);                                                       // 331
-        uint8_t m = 1;
-        if (ridx >= a.rrx && ridx < a.rrx + a.rw) {                                            // 332
-            const int R = a.dr[(size_t)frame * a.dr_frame + (size_t)gy * a.dr_step + ridx];
-            if (abs(L + R) < a.thresh) {                                                       // 334
-                cval = fminf(cval, a.conf_r[(size_t)frame * a.cr_frame + (size_t)cy * a.cr_pitch + (ridx - a.rrx)]);
-                m = 2;
-            } else { cval = 0.0f; m = 3; }
-        }
-        cval = __fmul_rn(255.0f, cval);                                                        // 209
-        if (a.mask && frame == 0) a.mask[(size_t)gy * a.mask_step + gx] = m;
-        if (a.plane_c) {
-            const size_t po = (size_t)frame * a.p_frame + (size_t)cy * a.pitch + cx;
-            a.plane_c[po] = cval;
-            a.plane_dc[po] = __fmul_rn(cval, (float)L);                                        // 289-290
-        }
-    } else if (a.mask && frame == 0) a.mask[(size_t)gy * a.mask_step + gx] = 0;
-    if (a.conf) a.conf[(size_t)frame * a.conf_frame + (size_t)gy * a.conf_step + gx] = cval;
+    if (a.out) a.out[(size_t)frame * a.out_frame + (size_t)i * a.out_step + j] = (int16_t)-16;
+    if (a.conf) a.conf[(size_t)frame * a.conf_frame + (size_t)i * a.conf_step + j] = 0.f;
+    if (a.mask && frame == 0) a.mask[(size_t)i * a.mask_step + j] = 0;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -166,17 +193,6 @@ __global__ void prep_noconf_kernel(const int16_t* __restrict__ disp, int64_t dst
     const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y, frame = blockIdx.z;
     if (j >= w) return;
     plane[(size_t)frame * pframe + (size_t)i * pitch + j] = (float)disp[(size_t)frame * dframe + (size_t)i * dstep + j];
-}
-
-// output outside the ROI = 16*(min_disp-1) with min_disp forced to 0 (disparity_filters.cpp:149,254,284)
-// grid = (ceil(W/256), H, frames)
-__global__ void fill_outside_kernel(int16_t* __restrict__ out, int64_t ostep, int64_t oframe, int W, int H,
-                                    int rx, int ry, int rw, int rh)
-{
-    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y, frame = blockIdx.z;
-    if (j >= W) return;
-    if (i >= ry && i < ry + rh && j >= rx && j < rx + rw) return;
-    out[(size_t)frame * oframe + (size_t)i * ostep + j] = (int16_t)-16;
 }
 
 }  // namespace dwls

@@ -40,10 +40,10 @@ def algorithmic_bytes(n_roi, f_disp, f_view, cn, S=2, P=6):
         "hsolve_kernel": (4 + 8 * S) * n_roi,
         "vsolve_kernel": (4 + 8 * S) * n_roi,
         "vsolve_kernel<final>": (4 + 4 * S) * n_roi + 2 * n_roi,
-        "fill_outside_kernel": 2 * (f_view - n_roi),
+        "border_kernel": 2 * (f_view - n_roi),
     }
     total = per["conf_kernel<right>"] + per["conf_kernel<left+lrc>"] + per["weights_kernel"] + 3 * per["hsolve_kernel"] \
-        + 2 * per["vsolve_kernel"] + per["vsolve_kernel<final>"] + per["fill_outside_kernel"]
+        + 2 * per["vsolve_kernel"] + per["vsolve_kernel<final>"] + per["border_kernel"]
     return total, per
 
 
