@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <string>
 #include <vector>
@@ -16,6 +17,7 @@ using namespace dwls;
 
 struct dwls_ctx {
     int device = 0;
+    int num_sms = 148;
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;                         // second lane of the pipelined host-batch entry point
     std::string err;
@@ -111,6 +113,7 @@ dwls_status dwls_ctx_create(int device, dwls_ctx** out)
         delete ctx;
         return DWLS_CUDA_ERROR;
     }
+    cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device);
     *out = ctx;
     return DWLS_OK;
 }
@@ -189,31 +192,93 @@ static bool plan_solver(int w, int h, SolvePlan* p)
     if (p->hK > 1024) return false;
     if (h <= 9 * 128) { p->vM = 9; p->vCols = 8; }
     else if (h <= 17 * 128) { p->vM = 17; p->vCols = 4; }
-    else if (h <= 17 * 256) { p->vM = 17; p->vCols = 2; }
     else return false;
     p->vK = round_up((h + p->vM - 1) / p->vM, 32);
     return true;
 }
 
-template <int S>
-static dwls_status launch_h(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
+template <int S, int MAXT>
+static dwls_status launch_h_inst(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
-    const size_t smem = sizeof(float) * (4 + 2 * S) * l2pad_size(pl.hK);
+    const size_t smem = hsolve_smem_bytes<S>(pl.hK, a.pitch);
+    auto k = hsolve_kernel<S, MAXT>;
+    static int ctas_per_sm = 0, cached_K = 0; static size_t cached_smem = 0;
+    if (smem > 227 * 1024) return fail(ctx, DWLS_UNSUPPORTED, "row too wide for the shared-memory stages of the row pass");
+    if (!ctas_per_sm || cached_K != pl.hK || cached_smem != smem) {
+        CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k, pl.hK, smem));
+        if (ctas_per_sm < 1) return fail(ctx, DWLS_CUDA_ERROR, "row pass does not fit on an SM");
+        cached_K = pl.hK; cached_smem = smem;
+    }
+    const int rows_total = a.h * frames;
+    int grid = ctx->num_sms * ctas_per_sm;
+    if (grid > rows_total) grid = rows_total;
     KTimer kt_(ctx, K_HSOLVE, st);
-    if (pl.hK <= 256) hsolve_kernel<S, 256><<<dim3(a.h, frames), pl.hK, smem, st>>>(a);
-    else if (pl.hK <= 512) hsolve_kernel<S, 512><<<dim3(a.h, frames), pl.hK, smem, st>>>(a);
-    else hsolve_kernel<S, 1024><<<dim3(a.h, frames), pl.hK, smem, st>>>(a);
+    k<<<grid, pl.hK, smem, st>>>(a, rows_total);
     CK(cudaGetLastError());
     return DWLS_OK;
 }
 
-template <int M, int S, int COLS, int FIN, int MAXT>
+template <int S>
+static dwls_status launch_h(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
+{
+    if (pl.hK <= 256) return launch_h_inst<S, 256>(ctx, a, pl, frames, st);
+    if (pl.hK <= 512) return launch_h_inst<S, 512>(ctx, a, pl, frames, st);
+    return launch_h_inst<S, 1024>(ctx, a, pl, frames, st);
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+
+// 2-D fp32 tensor [rows][pitch] with a (box_rows x box_cols) tile
+static dwls_status make_tmap(dwls_ctx* ctx, CUtensorMap* tm, const float* base, int pitch, int64_t rows, int box_cols, int box_rows)
+{
+    if (!g_encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
+        if (!fn || q != cudaDriverEntryPointSuccess) return fail(ctx, DWLS_CUDA_ERROR, "cuTensorMapEncodeTiled is not available in this driver");
+        g_encode = (EncodeTiledFn)fn;
+    }
+    const cuuint64_t dims[2] = { (cuuint64_t)pitch, (cuuint64_t)rows };
+    const cuuint64_t strides[1] = { (cuuint64_t)pitch * sizeof(float) };
+    const cuuint32_t box[2] = { (cuuint32_t)box_cols, (cuuint32_t)box_rows };
+    const cuuint32_t estr[2] = { 1, 1 };
+    const CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char b_[128];
+        snprintf(b_, sizeof b_, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+        ctx->err = b_;
+        return DWLS_CUDA_ERROR;
+    }
+    return DWLS_OK;
+}
+
+template <int M, int S, int VC, int FIN, int MAXT>
 static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
-    const size_t smem = sizeof(float) * COLS * (4 + 2 * S) * l2pad_size(pl.vK);
-    auto k = vsolve_kernel<M, S, COLS, FIN, MAXT>;
-    if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    TIMED(FIN == FIN_FLOAT ? K_VSOLVE : K_VSOLVE_FIN, st, k<<<dim3((a.w + COLS - 1) / COLS, frames), COLS * pl.vK, smem, st>>>(a));
+    VTma g;
+    g.nb = (a.h + 255) / 256;
+    g.rb = round_up((a.h + g.nb - 1) / g.nb, 128 / (VC * 4));     // every TMA box must land on a 128-byte boundary in smem
+    g.strips_x = (a.w + VC - 1) / VC;
+    g.strips_total = g.strips_x * frames;
+    const size_t smem = vsolve_smem_bytes<S, VC>(pl.vK, g.nb * g.rb);
+    if (smem > 227 * 1024) return fail(ctx, DWLS_UNSUPPORTED, "image too tall for the shared-memory stage of the column pass");
+    auto k = vsolve_kernel<M, S, VC, FIN, MAXT>;
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CUtensorMap tw, t0, t1;
+    dwls_status s;
+    const int64_t rows = (int64_t)frames * a.h;           // frames are contiguous planes: a.p_frame == a.w_frame == pitch * h
+    if ((s = make_tmap(ctx, &tw, a.weight, a.pitch, rows, VC, g.rb))) return s;
+    if ((s = make_tmap(ctx, &t0, a.in[0], a.pitch, rows, VC, g.rb))) return s;
+    if (S > 1) { if ((s = make_tmap(ctx, &t1, a.in[1], a.pitch, rows, VC, g.rb))) return s; }
+    else t1 = t0;
+    int grid = ctx->num_sms;
+    if (grid > g.strips_total) grid = g.strips_total;
+    TIMED(FIN == FIN_FLOAT ? K_VSOLVE : K_VSOLVE_FIN, st, k<<<grid, VC * pl.vK, smem, st>>>(a, g, tw, t0, t1));
     CK(cudaGetLastError());
     return DWLS_OK;
 }
@@ -223,7 +288,7 @@ static dwls_status launch_v(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& 
 {
     if (pl.vM == 9) return launch_v_inst<9, S, 8, FIN, 1024>(ctx, a, pl, frames, st);
     if (pl.vCols == 4) return launch_v_inst<17, S, 4, FIN, 512>(ctx, a, pl, frames, st);
-    return launch_v_inst<17, S, 2, FIN, 512>(ctx, a, pl, frames, st);
+    return fail(ctx, DWLS_UNSUPPORTED, "column pass supports at most 2176 rows");
 }
 
 // num_iter x (row pass, column pass, lambda *= attenuation) on S <= 2 planes sharing the weights
@@ -305,7 +370,7 @@ static dwls_status make_geom(dwls_ctx* ctx, int dw, int dh, int W, int H, int vc
             return fail(ctx, DWLS_BAD_SIZE, "upscaled ROI does not fit inside the view");
     }
     g->pitch = round_up(g->fw, 8);
-    if (!plan_solver(g->fw, g->fh, &g->plan)) return fail(ctx, DWLS_UNSUPPORTED, "ROI larger than 8192 x 4352 is not supported by the on-chip solver");
+    if (!plan_solver(g->fw, g->fh, &g->plan)) return fail(ctx, DWLS_UNSUPPORTED, "ROI larger than 8192 x 2176 is not supported by the on-chip solver");
     return DWLS_OK;
 }
 
@@ -593,7 +658,7 @@ static dwls_status fgs_dev_impl(dwls_ctx* ctx, const dwls_image* guide, const dw
 {
     const int w = guide->cols, h = guide->rows, pitch = round_up(w, 8);
     SolvePlan pl;
-    if (!plan_solver(w, h, &pl)) return fail(ctx, DWLS_UNSUPPORTED, "images larger than 8192 x 4352 are not supported by the on-chip solver");
+    if (!plan_solver(w, h, &pl)) return fail(ctx, DWLS_UNSUPPORTED, "images larger than 8192 x 2176 are not supported by the on-chip solver");
     const size_t plane = (size_t)pitch * h;
     const int S = src ? src->channels : 0;
     dwls_status s;

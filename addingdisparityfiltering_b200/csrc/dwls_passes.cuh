@@ -5,6 +5,7 @@
 // Algorithmic traffic per sweep and pixel: 4 B weight + 4*S B read + 4*S B write; the Thomas
 // intermediates the reference spills to interD (fgs_filter.cpp:75) never leave the SM.
 #pragma once
+#include <cuda.h>
 #include "dwls_solver.cuh"
 
 namespace dwls {
@@ -51,157 +52,247 @@ __device__ __forceinline__ float wls_normalise(float dc, float c)
 }
 
 // ---------------------------------------------------------------------------------------------
-// row pass: one CTA per image row, blockDim.x = K threads (multiple of 32, K*8 >= w)
-// grid = (h, frames)
+// row pass: persistent CTAs, each loops over image rows (row index runs over all frames of the
+// launch).  blockDim.x = K threads (multiple of 32, K*8 >= w); thread t owns columns [8t, 8t+8).
+// The weight row and the S plane rows of the NEXT rows are fetched by the TMA engine
+// (cp.async.bulk, completion on an mbarrier) into a ring of HST shared-memory stages while the
+// current row is being solved from registers, so bytes in flight do not depend on occupancy.
+// grid = (min(rows_total, CTAs that fit), 1)
+// dynamic smem = HST * (1+S) * pitch floats | 2 * (4+2S) * l2pad_size(K) floats | HST mbarriers
 // ---------------------------------------------------------------------------------------------
-template <int S, int MAXT>
-__global__ void __launch_bounds__(MAXT) hsolve_kernel(const SolveArgs a)
-{
-    extern __shared__ float sm[];
-    const int K = blockDim.x, M2 = K >> 5, KP = l2pad_size(K);
-    float* A = sm; float* B = A + KP; float* Bd = B + KP; float* C = Bd + KP;
-    float* F = C + KP; float* Fd = F + S * KP;
-    const int t = threadIdx.x, row = blockIdx.x, frame = blockIdx.y;
-    const int j0 = t * HM;
-    const size_t roff = (size_t)row * a.pitch + j0;
-    const float* W = a.weight + (size_t)frame * a.w_frame + roff;
+constexpr int HST = 3;
 
-    float c[HM], v[HM], f[S][HM];
-    float aprev = 0.f;
-    if (j0 < a.w) {
-        const float4 c0 = __ldg((const float4*)W), c1 = __ldg((const float4*)W + 1);
-        c[0] = c0.x; c[1] = c0.y; c[2] = c0.z; c[3] = c0.w; c[4] = c1.x; c[5] = c1.y; c[6] = c1.z; c[7] = c1.w;
-        if (t > 0) aprev = a.lam * __ldg(W - 1);
+template <int S>
+__host__ __device__ inline size_t hsolve_smem_bytes(int K, int pitch)
+{
+    return sizeof(float) * ((size_t)HST * (1 + S) * pitch + 2 * (size_t)(4 + 2 * S) * l2pad_size(K)) + sizeof(uint64_t) * HST;
+}
+
+template <int S, int MAXT>
+__global__ void __launch_bounds__(MAXT) hsolve_kernel(const SolveArgs a, const int rows_total)
+{
+    extern __shared__ __align__(128) float sm[];
+    const int K = blockDim.x, M2 = K >> 5, KP = l2pad_size(K);
+    const int t = threadIdx.x, j0 = t * HM;
+    float* stage0 = sm;                                           // [HST][1+S][pitch]
+    float* l2base = sm + (size_t)HST * (1 + S) * a.pitch;         // [2][(4+2S)*KP]
+    uint64_t* full = (uint64_t*)(l2base + 2 * (4 + 2 * S) * KP);  // [HST]
+    const uint32_t row_bytes = (uint32_t)a.pitch * 4u;
+    const int n_mine = (rows_total - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+    auto issue = [&](int i) {                                     // thread 0 only: fetch my i-th row into stage i % HST
+        const int gr = blockIdx.x + i * gridDim.x, frame = gr / a.h, row = gr - frame * a.h;
+        float* dst = stage0 + (size_t)(i % HST) * (1 + S) * a.pitch;
+        uint64_t* bar = full + (i % HST);
+        mbar_arrive_expect_tx(bar, (1 + S) * row_bytes);
+        bulk_g2s(dst, a.weight + (size_t)frame * a.w_frame + (size_t)row * a.pitch, row_bytes, bar);
 #pragma unroll
-        for (int s = 0; s < S; ++s) {
-            const float* P = a.in[s] + (size_t)frame * a.p_frame + roff;
-            const float4 f0 = *(const float4*)P, f1 = *((const float4*)P + 1);
-            f[s][0] = f0.x; f[s][1] = f0.y; f[s][2] = f0.z; f[s][3] = f0.w; f[s][4] = f1.x; f[s][5] = f1.y; f[s][6] = f1.z; f[s][7] = f1.w;
-        }
+        for (int s = 0; s < S; ++s)
+            bulk_g2s(dst + (size_t)(1 + s) * a.pitch, a.in[s] + (size_t)frame * a.p_frame + (size_t)row * a.pitch, row_bytes, bar);
+    };
+
+    if (t == 0) {
+        for (int i = 0; i < HST; ++i) mbar_init(full + i, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (t == 0)
+        for (int i = 0; i < HST && i < n_mine; ++i) issue(i);
+
+    for (int i = 0; i < n_mine; ++i) {
+        const int gr = blockIdx.x + i * gridDim.x, frame = gr / a.h, row = gr - frame * a.h;
+        const float* st = stage0 + (size_t)(i % HST) * (1 + S) * a.pitch;
+        float* A = l2base + (size_t)(i & 1) * (4 + 2 * S) * KP;
+        float* B = A + KP; float* Bd = B + KP; float* C = Bd + KP; float* F = C + KP; float* Fd = F + S * KP;
+        mbar_wait(full + (i % HST), (uint32_t)((i / HST) & 1));
+
+        float c[HM], v[HM], f[S][HM];
+        float aprev = 0.f;
+        if (j0 < a.w) {
+            const float4 c0 = *(const float4*)(st + j0), c1 = *(const float4*)(st + j0 + 4);
+            c[0] = c0.x; c[1] = c0.y; c[2] = c0.z; c[3] = c0.w; c[4] = c1.x; c[5] = c1.y; c[6] = c1.z; c[7] = c1.w;
+            if (t > 0) aprev = a.lam * st[j0 - 1];
 #pragma unroll
-        for (int i = 0; i < HM; ++i) {
-            c[i] = (j0 + i < a.w - 1) ? a.lam * c[i] : 0.f;      // last weight of a line is 0 (fgs_filter.cpp:614)
-            if (j0 + i >= a.w) {
+            for (int s = 0; s < S; ++s) {
+                const float* P = st + (size_t)(1 + s) * a.pitch + j0;
+                const float4 f0 = *(const float4*)P, f1 = *(const float4*)(P + 4);
+                f[s][0] = f0.x; f[s][1] = f0.y; f[s][2] = f0.z; f[s][3] = f0.w; f[s][4] = f1.x; f[s][5] = f1.y; f[s][6] = f1.z; f[s][7] = f1.w;
+            }
 #pragma unroll
-                for (int s = 0; s < S; ++s) f[s][i] = 0.f;
+            for (int k = 0; k < HM; ++k) {
+                c[k] = (j0 + k < a.w - 1) ? a.lam * c[k] : 0.f;      // last weight of a line is 0 (fgs_filter.cpp:614)
+                if (j0 + k >= a.w) {
+#pragma unroll
+                    for (int s = 0; s < S; ++s) f[s][k] = 0.f;
+                }
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < HM; ++k) {
+                c[k] = 0.f;
+#pragma unroll
+                for (int s = 0; s < S; ++s) f[s][k] = 0.f;
             }
         }
-    } else {
+        const Level1Out<HM, S> o = level1_reduce<HM, S>(c, f, v, aprev);
+        const int p = l2pad(t);
+        A[p] = o.A; B[p] = o.B;
 #pragma unroll
-        for (int i = 0; i < HM; ++i) {
-            c[i] = 0.f;
+        for (int s = 0; s < S; ++s) F[s * KP + p] = o.Fs[s];
+        if (t > 0) {
+            const int pm = l2pad(t - 1);
+            C[pm] = o.Cn; Bd[pm] = o.dB;
 #pragma unroll
-            for (int s = 0; s < S; ++s) f[s][i] = 0.f;
+            for (int s = 0; s < S; ++s) Fd[s * KP + pm] = o.dF[s];
         }
-    }
-    const Level1Out<HM, S> o = level1_reduce<HM, S>(c, f, v, aprev);
-    const int p = l2pad(t);
-    A[p] = o.A; B[p] = o.B;
+        if (t == K - 1) {
+            C[p] = 0.f; Bd[p] = 0.f;
 #pragma unroll
-    for (int s = 0; s < S; ++s) F[s * KP + p] = o.Fs[s];
-    if (t > 0) {
-        const int pm = l2pad(t - 1);
-        C[pm] = o.Cn; Bd[pm] = o.dB;
+            for (int s = 0; s < S; ++s) Fd[s * KP + p] = 0.f;
+        }
+        __syncthreads();                       // level-2 rows complete; every thread is done reading this stage
+        if (t == 0 && i + HST < n_mine) issue(i + HST);
+        if (t < 32) level2_solve_warp<S>(A, B, Bd, C, F, Fd, KP, M2, t);
+        __syncthreads();
+        float Uown[S], Uprev[S];
 #pragma unroll
-        for (int s = 0; s < S; ++s) Fd[s * KP + pm] = o.dF[s];
-    }
-    if (t == K - 1) {
-        C[p] = 0.f; Bd[p] = 0.f;
+        for (int s = 0; s < S; ++s) { Uown[s] = F[s * KP + p]; Uprev[s] = (t > 0) ? F[s * KP + l2pad(t - 1)] : 0.f; }
+        level1_fixup<HM, S>(c, f, v, Uprev, Uown);
+        if (j0 < a.w) {
 #pragma unroll
-        for (int s = 0; s < S; ++s) Fd[s * KP + p] = 0.f;
-    }
-    __syncthreads();
-    if (t < 32) level2_solve_warp<S>(A, B, Bd, C, F, Fd, KP, M2, t);
-    __syncthreads();
-    float Uown[S], Uprev[S];
-#pragma unroll
-    for (int s = 0; s < S; ++s) { Uown[s] = F[s * KP + p]; Uprev[s] = (t > 0) ? F[s * KP + l2pad(t - 1)] : 0.f; }
-    level1_fixup<HM, S>(c, f, v, Uprev, Uown);
-    if (j0 < a.w) {
-#pragma unroll
-        for (int s = 0; s < S; ++s) {
-            float* P = a.out[s] + (size_t)frame * a.p_frame + roff;
-            *(float4*)P = make_float4(f[s][0], f[s][1], f[s][2], f[s][3]);
-            *((float4*)P + 1) = make_float4(f[s][4], f[s][5], f[s][6], f[s][7]);
+            for (int s = 0; s < S; ++s) {
+                float* P = a.out[s] + (size_t)frame * a.p_frame + (size_t)row * a.pitch + j0;
+                *(float4*)P = make_float4(f[s][0], f[s][1], f[s][2], f[s][3]);
+                *((float4*)P + 1) = make_float4(f[s][4], f[s][5], f[s][6], f[s][7]);
+            }
         }
     }
 }
 
 // ---------------------------------------------------------------------------------------------
-// column pass: one CTA per strip of COLS adjacent columns; thread (x = tid % COLS, k = tid / COLS)
-// owns rows [k*M, k*M+M) of column x0+x.  blockDim.x = COLS * K, K multiple of 32, K*M >= h.
-// grid = (ceil(w / COLS), frames)
+// column pass: persistent CTAs (one per SM), each loops over strips of VC adjacent columns (8; 4 or 2 for tall images)
+// (strip index runs over all frames of the launch).  Thread (x = tid % 8, k = tid / 8) owns rows
+// [k*M, k*M+M) of column x of the strip.  A strip (h rows x 32 bytes, for the weight plane and
+// the S data planes) is fetched as 2-D TMA tiles into ONE shared-memory stage; every thread pulls
+// its M rows into registers (bank-conflict free because M is odd), after which the stage is
+// released and the TMA engine fetches the next strip while this one is solved and stored.
+// Every global access is therefore full 32-byte sectors, and neighbouring strips (the other
+// sectors of the same 128-byte lines) are in flight on other SMs at the same time.
+// blockDim.x = 8 * K, K multiple of 32, K*M >= h.   grid = min(#strips, #SMs)
+// dynamic smem = (1+S) * rows_staged * 8 floats | 8 * (4+2S) * l2pad_size(K) floats | mbarrier
 // ---------------------------------------------------------------------------------------------
-template <int M, int S, int COLS, int FIN, int MAXT>
-__global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a)
+struct VTma {
+    int rb;            // rows per TMA box (<= 256)
+    int nb;            // boxes per strip: nb * rb >= h
+    int strips_x;      // strips per frame = ceil(w / VC)
+    int strips_total;  // strips_x * frames
+};
+
+template <int S, int VC>
+__host__ __device__ inline size_t vsolve_smem_bytes(int K, int rows_staged)
 {
-    extern __shared__ float sm[];
-    const int K = blockDim.x / COLS, M2 = K >> 5, KP = l2pad_size(K);
-    const int SYS = (4 + 2 * S) * KP;                       // floats per reduced system
-    const int t = threadIdx.x, x = t % COLS, k = t / COLS, frame = blockIdx.y;
-    const int col = blockIdx.x * COLS + x, r0 = k * M;
-    float* A = sm + x * SYS; float* B = A + KP; float* Bd = B + KP; float* C = Bd + KP;
+    return sizeof(float) * ((size_t)(1 + S) * rows_staged * VC + (size_t)VC * (4 + 2 * S) * l2pad_size(K)) + 16;
+}
+
+template <int M, int S, int VC, int FIN, int MAXT>
+__global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const VTma g, const __grid_constant__ CUtensorMap tm_w,
+                                                      const __grid_constant__ CUtensorMap tm_p0, const __grid_constant__ CUtensorMap tm_p1)
+{
+    extern __shared__ __align__(128) float sm[];
+    const int K = blockDim.x / VC, M2 = K >> 5, KP = l2pad_size(K);
+    const int SYS = (4 + 2 * S) * KP;
+    const int rows_staged = g.nb * g.rb;
+    float* stage = sm;                                            // [1+S][rows_staged][8]
+    float* l2base = sm + (size_t)(1 + S) * rows_staged * VC;      // [8][SYS]
+    uint64_t* full = (uint64_t*)(l2base + (size_t)VC * SYS);
+    const int t = threadIdx.x, x = t % VC, k = t / VC, r0 = k * M;
+    float* A = l2base + x * SYS; float* B = A + KP; float* Bd = B + KP; float* C = Bd + KP;
     float* F = C + KP; float* Fd = F + S * KP;
-    const bool live = col < a.w;
-    const size_t off0 = (size_t)r0 * a.pitch + col;
-    const float* W = a.weight + (size_t)frame * a.w_frame + off0;
+    const int n_mine = (g.strips_total - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const uint32_t tx_bytes = (uint32_t)((1 + S) * rows_staged * VC * sizeof(float));
 
-    float c[M], v[M], f[S][M];
-    float aprev = 0.f;
-#pragma unroll
-    for (int i = 0; i < M; ++i) {
-        const bool in = live && (r0 + i < a.h);
-        c[i] = (live && (r0 + i < a.h - 1)) ? a.lam * __ldg(W + (size_t)i * a.pitch) : 0.f;   // last row weight 0 (658-660)
-#pragma unroll
-        for (int s = 0; s < S; ++s) f[s][i] = in ? a.in[s][(size_t)frame * a.p_frame + off0 + (size_t)i * a.pitch] : 0.f;
-    }
-    if (live && k > 0 && r0 - 1 < a.h - 1) aprev = a.lam * __ldg(W - a.pitch);
-
-    const Level1Out<M, S> o = level1_reduce<M, S>(c, f, v, aprev);
-    const int p = l2pad(k);
-    A[p] = o.A; B[p] = o.B;
-#pragma unroll
-    for (int s = 0; s < S; ++s) F[s * KP + p] = o.Fs[s];
-    if (k > 0) {
-        const int pm = l2pad(k - 1);
-        C[pm] = o.Cn; Bd[pm] = o.dB;
-#pragma unroll
-        for (int s = 0; s < S; ++s) Fd[s * KP + pm] = o.dF[s];
-    }
-    if (k == K - 1) {
-        C[p] = 0.f; Bd[p] = 0.f;
-#pragma unroll
-        for (int s = 0; s < S; ++s) Fd[s * KP + p] = 0.f;
-    }
-    __syncthreads();
-    {
-        const int warp = t >> 5, nwarps = blockDim.x >> 5, lane = t & 31;
-        for (int sys = warp; sys < COLS; sys += nwarps) {
-            float* A2 = sm + sys * SYS;
-            level2_solve_warp<S>(A2, A2 + KP, A2 + 2 * KP, A2 + 3 * KP, A2 + 4 * KP, A2 + (4 + S) * KP, KP, M2, lane);
+    auto issue = [&](int i) {                                     // thread 0: fetch my i-th strip
+        const int si = blockIdx.x + i * gridDim.x, frame = si / g.strips_x, col0 = (si - frame * g.strips_x) * VC;
+        mbar_arrive_expect_tx(full, tx_bytes);
+        for (int b = 0; b < g.nb; ++b) {
+            const int grow = frame * a.h + b * g.rb;
+            tma_load_2d(stage + (size_t)b * g.rb * VC, &tm_w, col0, grow, full);
+            tma_load_2d(stage + (size_t)(rows_staged + b * g.rb) * VC, &tm_p0, col0, grow, full);
+            if (S > 1) tma_load_2d(stage + (size_t)(2 * rows_staged + b * g.rb) * VC, &tm_p1, col0, grow, full);
         }
-    }
+    };
+
+    if (t == 0) { mbar_init(full, 1); mbar_fence_init(); }
     __syncthreads();
-    float Uown[S], Uprev[S];
+    if (t == 0 && n_mine > 0) issue(0);
+
+    for (int i = 0; i < n_mine; ++i) {
+        const int si = blockIdx.x + i * gridDim.x, frame = si / g.strips_x, col = (si - frame * g.strips_x) * VC + x;
+        const bool live = col < a.w;
+        mbar_wait(full, (uint32_t)(i & 1));
+        float c[M], v[M], f[S][M];
+        float aprev = 0.f;
+        {
+            const float* sw = stage + (size_t)r0 * VC + x;
 #pragma unroll
-    for (int s = 0; s < S; ++s) { Uown[s] = F[s * KP + p]; Uprev[s] = (k > 0) ? F[s * KP + l2pad(k - 1)] : 0.f; }
-    level1_fixup<M, S>(c, f, v, Uprev, Uown);
-    if (!live) return;
-    if (FIN == FIN_FLOAT) {
+            for (int m = 0; m < M; ++m) {
+                const bool in = live && (r0 + m < a.h);
+                c[m] = (live && (r0 + m < a.h - 1)) ? a.lam * sw[m * VC] : 0.f;                  // last row weight 0 (fgs_filter.cpp:658-660)
 #pragma unroll
-        for (int i = 0; i < M; ++i)
-            if (r0 + i < a.h) {
-#pragma unroll
-                for (int s = 0; s < S; ++s) a.out[s][(size_t)frame * a.p_frame + off0 + (size_t)i * a.pitch] = f[s][i];
+                for (int s = 0; s < S; ++s) f[s][m] = in ? sw[(size_t)(1 + s) * rows_staged * VC + m * VC] : 0.f;
             }
-    } else {
-        int16_t* O = a.out16 + (size_t)frame * a.out16_frame + (size_t)r0 * a.out16_step + col;
+            if (live && k > 0 && r0 - 1 < a.h - 1) aprev = a.lam * sw[-VC];
+        }
+        const Level1Out<M, S> o = level1_reduce<M, S>(c, f, v, aprev);
+        const int p = l2pad(k);
+        A[p] = o.A; B[p] = o.B;
 #pragma unroll
-        for (int i = 0; i < M; ++i)
-            if (r0 + i < a.h) {
-                const float val = (FIN == FIN_WLS) ? wls_normalise(f[0][i], f[S - 1][i]) : f[0][i];
-                O[(size_t)i * a.out16_step] = cvt_s16(val);
+        for (int s = 0; s < S; ++s) F[s * KP + p] = o.Fs[s];
+        if (k > 0) {
+            const int pm = l2pad(k - 1);
+            C[pm] = o.Cn; Bd[pm] = o.dB;
+#pragma unroll
+            for (int s = 0; s < S; ++s) Fd[s * KP + pm] = o.dF[s];
+        }
+        if (k == K - 1) {
+            C[p] = 0.f; Bd[p] = 0.f;
+#pragma unroll
+            for (int s = 0; s < S; ++s) Fd[s * KP + p] = 0.f;
+        }
+        __syncthreads();                       // level-2 rows complete; the stage has been read by everyone
+        if (t == 0 && i + 1 < n_mine) issue(i + 1);
+        {
+            const int warp = t >> 5, nwarps = blockDim.x >> 5, lane = t & 31;
+            for (int sys = warp; sys < VC; sys += nwarps) {
+                float* A2 = l2base + sys * SYS;
+                level2_solve_warp<S>(A2, A2 + KP, A2 + 2 * KP, A2 + 3 * KP, A2 + 4 * KP, A2 + (4 + S) * KP, KP, M2, lane);
             }
+        }
+        __syncthreads();
+        float Uown[S], Uprev[S];
+#pragma unroll
+        for (int s = 0; s < S; ++s) { Uown[s] = F[s * KP + p]; Uprev[s] = (k > 0) ? F[s * KP + l2pad(k - 1)] : 0.f; }
+        __syncthreads();                       // level-2 scratch may be overwritten by the next strip from here on
+        level1_fixup<M, S>(c, f, v, Uprev, Uown);
+        if (live) {
+            const size_t off0 = (size_t)r0 * a.pitch + col;
+            if (FIN == FIN_FLOAT) {
+#pragma unroll
+                for (int m = 0; m < M; ++m)
+                    if (r0 + m < a.h) {
+#pragma unroll
+                        for (int s = 0; s < S; ++s) a.out[s][(size_t)frame * a.p_frame + off0 + (size_t)m * a.pitch] = f[s][m];
+                    }
+            } else {
+                int16_t* O = a.out16 + (size_t)frame * a.out16_frame + (size_t)r0 * a.out16_step + col;
+#pragma unroll
+                for (int m = 0; m < M; ++m)
+                    if (r0 + m < a.h) {
+                        const float val = (FIN == FIN_WLS) ? wls_normalise(f[0][m], f[S - 1][m]) : f[0][m];
+                        O[(size_t)m * a.out16_step] = cvt_s16(val);
+                    }
+            }
+        }
     }
 }
 
