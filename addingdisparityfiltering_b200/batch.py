@@ -97,5 +97,6 @@ def gather_results(local_out, group=None):
     import torch.distributed as dist
     world = dist.get_world_size(group)
     full = torch.empty((world * local_out.shape[0],) + tuple(local_out.shape[1:]), dtype=local_out.dtype, device=local_out.device)
-    dist.all_gather_into_tensor(full, local_out.contiguous(), group=group)
+    # gathered as raw bytes: the collective only moves data, and gloo has no int16 kernels
+    dist.all_gather_into_tensor(full.view(torch.uint8), local_out.contiguous().view(torch.uint8), group=group)
     return full

@@ -4,7 +4,7 @@ G1 restates MakeArtificialExample of the reference's perf test
 (modules/ximgproc/perf/perf_disparity_wls_filter.cpp:95-167): flat background and a centred
 foreground rectangle at disparity 0.15*w, additive Gaussian noise (sigma 6) on the guide and on
 both disparity maps, ROI = (0.15*w, 0, w-0.15*w, h).  numpy's generator replaces cv::RNG, so the
-pixel values differ from an OpenCV run but the oracle and the GPU always see identical arrays.
+pixel values differ from an OpenCV run but the CPU checker and the GPU always see identical arrays.
 """
 import numpy as np
 
