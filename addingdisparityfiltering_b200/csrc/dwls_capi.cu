@@ -317,10 +317,10 @@ static dwls_status run_sweeps(dwls_ctx* ctx, SolveArgs a, const float* chor, con
 static dwls_status launch_weights(dwls_ctx* ctx, const uint8_t* guide, int64_t gstep, int64_t gframe, int cn, int w, int h,
                                   int pitch, float* chor, float* cvert, int64_t wframe, int frames, cudaStream_t st)
 {
-    dim3 grid((pitch + 255) / 256, h, frames);
+    dim3 grid((pitch + WT_PX - 1) / WT_PX, h, frames);
     KTimer kt_(ctx, K_WEIGHTS, st);
-    if (cn == 1) weights_kernel<1><<<grid, 256, 0, st>>>(guide, gstep, gframe, w, h, pitch, ctx->lut, chor, cvert, wframe);
-    else weights_kernel<3><<<grid, 256, 0, st>>>(guide, gstep, gframe, w, h, pitch, ctx->lut, chor, cvert, wframe);
+    if (cn == 1) weights_kernel<1><<<grid, WT_T, 0, st>>>(guide, gstep, gframe, w, h, pitch, ctx->lut, chor, cvert, wframe);
+    else weights_kernel<3><<<grid, WT_T, 0, st>>>(guide, gstep, gframe, w, h, pitch, ctx->lut, chor, cvert, wframe);
     CK(cudaGetLastError());
     return DWLS_OK;
 }

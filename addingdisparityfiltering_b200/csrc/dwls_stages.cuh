@@ -24,29 +24,65 @@ __global__ void lut_kernel(float* lut, int n, float sigma)
 
 // ---------------------------------------------------------------------------------------------
 // weight planes (fgs_filter.cpp:593-616 horizontal, 625-661 vertical), guide = ROI view of the
-// 8-bit image.  One thread per pixel; columns w..pitch-1 are zero-filled.
-// grid = (ceil(pitch/256), h, frames)
+// 8-bit image.  A CTA handles WT_PX pixels of one row: the bytes of rows i and i+1 are staged in
+// shared memory with aligned 128-bit loads (the ROI view starts at an arbitrary byte), each
+// thread then forms the squared colour distances of 4 consecutive pixels, gathers the LUT and
+// writes two float4.  Columns w..pitch-1 are zero-filled.
+// grid = (ceil(pitch / WT_PX), h, frames)
 // ---------------------------------------------------------------------------------------------
+constexpr int WT_T = 256, WT_PX = 4 * WT_T;
+
 template <int CN>
-__global__ void __launch_bounds__(256) weights_kernel(const uint8_t* __restrict__ guide, int64_t gstep, int64_t gframe,
-                                                      int w, int h, int pitch, const float* __restrict__ lut,
-                                                      float* __restrict__ chor, float* __restrict__ cvert, int64_t wframe)
+__global__ void __launch_bounds__(WT_T) weights_kernel(const uint8_t* __restrict__ guide, int64_t gstep, int64_t gframe,
+                                                       int w, int h, int pitch, const float* __restrict__ lut,
+                                                       float* __restrict__ chor, float* __restrict__ cvert, int64_t wframe)
 {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y, frame = blockIdx.z;
-    if (j >= pitch) return;
-    const size_t o = (size_t)frame * wframe + (size_t)i * pitch + j;
-    if (j >= w) { chor[o] = 0.f; cvert[o] = 0.f; return; }
-    const uint8_t* g = guide + (size_t)frame * gframe + (size_t)i * gstep + (size_t)j * CN;
-    int dh = 0, dv = 0;
-    const bool hr = j + 1 < w, vr = i + 1 < h;
+    constexpr int ROWB = ((WT_PX + 1) * CN + 15 + 15) / 16 * 16;       // staged bytes per row incl. misalignment slack
+    __shared__ __align__(16) uint8_t sm[2][ROWB];
+    const int tid = threadIdx.x, i = blockIdx.y, frame = blockIdx.z, c0 = blockIdx.x * WT_PX;
+    const int npx = min(WT_PX + 1, w - c0);                             // pixels available from c0 on (incl. the right neighbour)
+    int mis[2] = { 0, 0 };
+    if (npx > 0) {
 #pragma unroll
-    for (int ch = 0; ch < CN; ++ch) {
-        const int p = g[ch];
-        if (hr) { const int t = p - (int)g[CN + ch]; dh += t * t; }
-        if (vr) { const int t = p - (int)g[gstep + ch]; dv += t * t; }
+        for (int rr = 0; rr < 2; ++rr) {
+            if (i + rr >= h) break;
+            const uint8_t* rp = guide + (size_t)frame * gframe + (size_t)(i + rr) * gstep + (size_t)c0 * CN;
+            mis[rr] = (int)((uintptr_t)rp & 15);
+            const uint4* base = (const uint4*)(rp - mis[rr]);           // an aligned 16-byte chunk holding >= 1 valid byte never crosses a page
+            const int nch = (mis[rr] + npx * CN + 15) >> 4;
+            for (int k = tid; k < nch; k += WT_T) ((uint4*)sm[rr])[k] = __ldg(base + k);
+        }
     }
-    chor[o] = hr ? __ldg(lut + dh) : 0.f;
-    cvert[o] = vr ? __ldg(lut + dv) : 0.f;
+    __syncthreads();
+    const int j0 = c0 + 4 * tid;
+    if (j0 >= pitch) return;
+    float ho[4] = { 0.f, 0.f, 0.f, 0.f }, vo[4] = { 0.f, 0.f, 0.f, 0.f };
+    if (j0 < w) {
+        const uint8_t* r0 = sm[0] + mis[0] + 4 * tid * CN;
+        const uint8_t* r1 = sm[1] + mis[1] + 4 * tid * CN;
+        const bool vr = i + 1 < h;
+        int px[5][CN];
+#pragma unroll
+        for (int q = 0; q < 5; ++q)
+#pragma unroll
+            for (int ch = 0; ch < CN; ++ch) px[q][ch] = (j0 + q < w) ? r0[q * CN + ch] : 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            if (j0 + q >= w) break;
+            int dh = 0, dv = 0;
+#pragma unroll
+            for (int ch = 0; ch < CN; ++ch) {
+                const int t = px[q][ch] - px[q + 1][ch];
+                dh += t * t;
+                if (vr) { const int u = px[q][ch] - (int)r1[q * CN + ch]; dv += u * u; }
+            }
+            ho[q] = (j0 + q + 1 < w) ? __ldg(lut + dh) : 0.f;           // Chor[i][w-1] = 0 (614)
+            vo[q] = vr ? __ldg(lut + dv) : 0.f;                          // Cvert[h-1][j] = 0 (658-660)
+        }
+    }
+    const size_t o = (size_t)frame * wframe + (size_t)i * pitch + j0;
+    *(float4*)(chor + o) = make_float4(ho[0], ho[1], ho[2], ho[3]);
+    *(float4*)(cvert + o) = make_float4(vo[0], vo[1], vo[2], vo[3]);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -111,10 +147,11 @@ __global__ void __launch_bounds__(CF_T) conf_kernel(const ConfArgs a)
             vin[i] = col[(size_t)reflect101(yb + i + r, a.rh) * sstep];
             vout[i] = col[(size_t)reflect101(yb + i - r, a.rh) * sstep];
         }
+        float cv[CF_PF];
 #pragma unroll
         for (int i = 0; i < CF_PF; ++i) {
-            const int y = yb + i;
-            if (y >= y1) break;                                     // uniform across the CTA
+            cv[i] = 0.f;
+            if (yb + i >= y1) break;                                // uniform across the CTA
             cs += vin[i]; cq += vin[i] * vin[i];
             const int buf = i & 1;                                  // CF_PF is even, so this alternates across chunks too
             cs_buf[buf][tid] = cs; cq_buf[buf][tid] = cq;
@@ -125,32 +162,50 @@ __global__ void __launch_bounds__(CF_T) conf_kernel(const ConfArgs a)
                 const float mean = __fmul_rn((float)s, a.scale_f);
                 const float meansq = (float)__dmul_rn((double)q, a.scale_d);
                 const float variance = __fsub_rn(meansq, __fmul_rn(mean, mean));
-                float cval = fmaxf(__fsub_rn(1.0f, __fmul_rn(a.roll_off, variance)), 0.0f);
-                if (!LEFT) {
-                    a.conf_r[(size_t)frame * a.cr_frame + (size_t)y * a.cr_pitch + cx] = cval;
-                } else {
-                    const int gx = a.rx + cx, gy = a.ry + y;
-                    const int L = col[(size_t)y * sstep];
-                    const int ridx = gx - (L >> 4);                                                   // 331
-                    uint8_t m = 1;
-                    if (ridx >= a.rrx && ridx < a.rrx + a.rw) {                                        // 332
-                        const int R = a.dr[(size_t)frame * a.dr_frame + (size_t)gy * a.dr_step + ridx];
-                        if (abs(L + R) < a.thresh) {                                                   // 334
-                            cval = fminf(cval, a.conf_r[(size_t)frame * a.cr_frame + (size_t)y * a.cr_pitch + (ridx - a.rrx)]);
-                            m = 2;
-                        } else { cval = 0.0f; m = 3; }
-                    }
-                    cval = __fmul_rn(255.0f, cval);                                                    // 209
-                    if (a.mask && frame == 0) a.mask[(size_t)gy * a.mask_step + gx] = m;
-                    if (a.plane_c) {
-                        const size_t po = (size_t)frame * a.p_frame + (size_t)y * a.pitch + cx;
-                        a.plane_c[po] = cval;
-                        a.plane_dc[po] = __fmul_rn(cval, (float)L);                                    // 289-290
-                    }
-                    if (a.conf) a.conf[(size_t)frame * a.conf_frame + (size_t)gy * a.conf_step + gx] = cval;
-                }
+                cv[i] = fmaxf(__fsub_rn(1.0f, __fmul_rn(a.roll_off, variance)), 0.0f);
             }
             cs -= vout[i]; cq -= vout[i] * vout[i];
+        }
+        if (!is_out) continue;
+        const int nrow = min(CF_PF, y1 - yb);
+        if (!LEFT) {
+#pragma unroll
+            for (int i = 0; i < CF_PF; ++i)
+                if (i < nrow) a.conf_r[(size_t)frame * a.cr_frame + (size_t)(yb + i) * a.cr_pitch + cx] = cv[i];
+        } else {
+            // left-right consistency for the CF_PF rows at once, so the dependent gathers of all rows are in flight together
+            const int gx = a.rx + cx;
+            int L[CF_PF], ridx[CF_PF], R[CF_PF];
+            float cr[CF_PF];
+            bool hit[CF_PF];
+#pragma unroll
+            for (int i = 0; i < CF_PF; ++i) L[i] = (i < nrow) ? col[(size_t)(yb + i) * sstep] : 0;
+#pragma unroll
+            for (int i = 0; i < CF_PF; ++i) {
+                ridx[i] = gx - (L[i] >> 4);                                                            // 331
+                hit[i] = i < nrow && ridx[i] >= a.rrx && ridx[i] < a.rrx + a.rw;                      // 332
+                R[i] = hit[i] ? a.dr[(size_t)frame * a.dr_frame + (size_t)(a.ry + yb + i) * a.dr_step + ridx[i]] : 0;
+                cr[i] = hit[i] ? a.conf_r[(size_t)frame * a.cr_frame + (size_t)(yb + i) * a.cr_pitch + (ridx[i] - a.rrx)] : 0.f;
+            }
+#pragma unroll
+            for (int i = 0; i < CF_PF; ++i) {
+                if (i >= nrow) break;
+                const int gy = a.ry + yb + i;
+                float cval = cv[i];
+                uint8_t m = 1;
+                if (hit[i]) {
+                    if (abs(L[i] + R[i]) < a.thresh) { cval = fminf(cval, cr[i]); m = 2; }              // 334-335
+                    else { cval = 0.0f; m = 3; }                                                        // 337
+                }
+                cval = __fmul_rn(255.0f, cval);                                                        // 209
+                if (a.mask && frame == 0) a.mask[(size_t)gy * a.mask_step + gx] = m;
+                if (a.plane_c) {
+                    const size_t po = (size_t)frame * a.p_frame + (size_t)(yb + i) * a.pitch + cx;
+                    a.plane_c[po] = cval;
+                    a.plane_dc[po] = __fmul_rn(cval, (float)L[i]);                                     // 289-290
+                }
+                if (a.conf) a.conf[(size_t)frame * a.conf_frame + (size_t)gy * a.conf_step + gx] = cval;
+            }
         }
     }
 }
