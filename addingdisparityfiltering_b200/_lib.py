@@ -11,7 +11,7 @@ import threading
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdwls_b200.so")
+LIB_PATH = os.environ.get("DWLS_LIB", os.path.join(_HERE, "libdwls_b200.so"))      # DWLS_LIB: tuning builds only
 CSRC = os.path.join(_HERE, "csrc")
 
 DWLS_OK, DWLS_BAD_ARG, DWLS_BAD_SIZE, DWLS_CUDA_ERROR, DWLS_UNSUPPORTED = 0, 1, 2, 3, 4

@@ -10,7 +10,10 @@
 
 namespace dwls {
 
-constexpr int HM = 8;        // elements per thread in the row solve (two float4)
+#ifndef DWLS_HM
+#define DWLS_HM 8
+#endif
+constexpr int HM = DWLS_HM;  // elements per thread in the row solve (HM/4 float4 per plane)
 constexpr int MAXS = 4;      // planes solved together (fgs_filter.cpp:184: channels <= 4)
 
 struct SolveArgs {
@@ -60,23 +63,35 @@ __device__ __forceinline__ float wls_normalise(float dc, float c)
 // grid = (min(rows_total, CTAs that fit), 1)
 // dynamic smem = HST * (1+S) * pitch floats | 2 * (4+2S) * l2pad_size(K) floats | HST mbarriers
 // ---------------------------------------------------------------------------------------------
-constexpr int HST = 3;
+#ifndef DWLS_HST
+#define DWLS_HST 2
+#endif
+#ifndef DWLS_HMINB
+#define DWLS_HMINB 4
+#endif
+#ifndef DWLS_HL2BUF
+#define DWLS_HL2BUF 1
+#endif
+constexpr int HL2BUF = DWLS_HL2BUF; // level-2 scratch copies (1 needs a third barrier per row, 2 does not)
+constexpr int HST = DWLS_HST;      // shared-memory stages per CTA
+constexpr int HMINB = DWLS_HMINB;  // CTAs per SM the row pass is compiled for (register cap)
 
 template <int S>
 __host__ __device__ inline size_t hsolve_smem_bytes(int K, int pitch)
 {
-    return sizeof(float) * ((size_t)HST * (1 + S) * pitch + 2 * (size_t)(4 + 2 * S) * l2pad_size(K)) + sizeof(uint64_t) * HST;
+    return sizeof(float) * ((size_t)HST * (1 + S) * pitch + HL2BUF * (size_t)(4 + 2 * S) * l2pad_size(K) + 32 * (2 + S) * HM) + sizeof(uint64_t) * HST;
 }
 
 template <int S, int MAXT>
-__global__ void __launch_bounds__(MAXT) hsolve_kernel(const SolveArgs a, const int rows_total)
+__global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? HMINB : 1)) hsolve_kernel(const SolveArgs a, const int rows_total)
 {
     extern __shared__ __align__(128) float sm[];
     const int K = blockDim.x, M2 = K >> 5, KP = l2pad_size(K);
     const int t = threadIdx.x, j0 = t * HM;
     float* stage0 = sm;                                           // [HST][1+S][pitch]
     float* l2base = sm + (size_t)HST * (1 + S) * a.pitch;         // [2][(4+2S)*KP]
-    uint64_t* full = (uint64_t*)(l2base + 2 * (4 + 2 * S) * KP);  // [HST]
+    float* stash = l2base + HL2BUF * (4 + 2 * S) * KP;                 // [(2+S)*HM][32]: warp 0 parks its level-1 state here during level 2
+    uint64_t* full = (uint64_t*)(stash + 32 * (2 + S) * HM);      // [HST]
     const uint32_t row_bytes = (uint32_t)a.pitch * 4u;
     const int n_mine = (rows_total - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
@@ -102,21 +117,27 @@ __global__ void __launch_bounds__(MAXT) hsolve_kernel(const SolveArgs a, const i
     for (int i = 0; i < n_mine; ++i) {
         const int gr = blockIdx.x + i * gridDim.x, frame = gr / a.h, row = gr - frame * a.h;
         const float* st = stage0 + (size_t)(i % HST) * (1 + S) * a.pitch;
-        float* A = l2base + (size_t)(i & 1) * (4 + 2 * S) * KP;
+        float* A = l2base + (size_t)(HL2BUF > 1 ? (i & 1) : 0) * (4 + 2 * S) * KP;
         float* B = A + KP; float* Bd = B + KP; float* C = Bd + KP; float* F = C + KP; float* Fd = F + S * KP;
         mbar_wait(full + (i % HST), (uint32_t)((i / HST) & 1));
 
         float c[HM], v[HM], f[S][HM];
         float aprev = 0.f;
         if (j0 < a.w) {
-            const float4 c0 = *(const float4*)(st + j0), c1 = *(const float4*)(st + j0 + 4);
-            c[0] = c0.x; c[1] = c0.y; c[2] = c0.z; c[3] = c0.w; c[4] = c1.x; c[5] = c1.y; c[6] = c1.z; c[7] = c1.w;
+#pragma unroll
+            for (int q = 0; q < HM / 4; ++q) {
+                const float4 cc = *(const float4*)(st + j0 + 4 * q);
+                c[4 * q] = cc.x; c[4 * q + 1] = cc.y; c[4 * q + 2] = cc.z; c[4 * q + 3] = cc.w;
+            }
             if (t > 0) aprev = a.lam * st[j0 - 1];
 #pragma unroll
             for (int s = 0; s < S; ++s) {
                 const float* P = st + (size_t)(1 + s) * a.pitch + j0;
-                const float4 f0 = *(const float4*)P, f1 = *(const float4*)(P + 4);
-                f[s][0] = f0.x; f[s][1] = f0.y; f[s][2] = f0.z; f[s][3] = f0.w; f[s][4] = f1.x; f[s][5] = f1.y; f[s][6] = f1.z; f[s][7] = f1.w;
+#pragma unroll
+                for (int q = 0; q < HM / 4; ++q) {
+                    const float4 ff = *(const float4*)(P + 4 * q);
+                    f[s][4 * q] = ff.x; f[s][4 * q + 1] = ff.y; f[s][4 * q + 2] = ff.z; f[s][4 * q + 3] = ff.w;
+                }
             }
 #pragma unroll
             for (int k = 0; k < HM; ++k) {
@@ -152,18 +173,34 @@ __global__ void __launch_bounds__(MAXT) hsolve_kernel(const SolveArgs a, const i
         }
         __syncthreads();                       // level-2 rows complete; every thread is done reading this stage
         if (t == 0 && i + HST < n_mine) issue(i + HST);
-        if (t < 32) level2_solve_warp<S>(A, B, Bd, C, F, Fd, KP, M2, t);
+        if (t < 32) {
+            // the level-2 warp needs its registers for the reduced system: park the level-1 state in shared memory meanwhile
+#pragma unroll
+            for (int k = 0; k < HM; ++k) {
+                stash[(k) * 32 + t] = c[k]; stash[(HM + k) * 32 + t] = v[k];
+#pragma unroll
+                for (int s = 0; s < S; ++s) stash[((2 + s) * HM + k) * 32 + t] = f[s][k];
+            }
+            level2_solve_warp<S>(A, B, Bd, C, F, Fd, KP, M2, t);
+#pragma unroll
+            for (int k = 0; k < HM; ++k) {
+                c[k] = stash[(k) * 32 + t]; v[k] = stash[(HM + k) * 32 + t];
+#pragma unroll
+                for (int s = 0; s < S; ++s) f[s][k] = stash[((2 + s) * HM + k) * 32 + t];
+            }
+        }
         __syncthreads();
         float Uown[S], Uprev[S];
 #pragma unroll
         for (int s = 0; s < S; ++s) { Uown[s] = F[s * KP + p]; Uprev[s] = (t > 0) ? F[s * KP + l2pad(t - 1)] : 0.f; }
+        if (HL2BUF == 1) __syncthreads();       // the single scratch copy is rewritten by the next row
         level1_fixup<HM, S>(c, f, v, Uprev, Uown);
         if (j0 < a.w) {
 #pragma unroll
             for (int s = 0; s < S; ++s) {
                 float* P = a.out[s] + (size_t)frame * a.p_frame + (size_t)row * a.pitch + j0;
-                *(float4*)P = make_float4(f[s][0], f[s][1], f[s][2], f[s][3]);
-                *((float4*)P + 1) = make_float4(f[s][4], f[s][5], f[s][6], f[s][7]);
+#pragma unroll
+                for (int q = 0; q < HM / 4; ++q) *((float4*)P + q) = make_float4(f[s][4 * q], f[s][4 * q + 1], f[s][4 * q + 2], f[s][4 * q + 3]);
             }
         }
     }
@@ -188,10 +225,10 @@ struct VTma {
     int strips_total;  // strips_x * frames
 };
 
-template <int S, int VC>
+template <int M, int S, int VC>
 __host__ __device__ inline size_t vsolve_smem_bytes(int K, int rows_staged)
 {
-    return sizeof(float) * ((size_t)(1 + S) * rows_staged * VC + (size_t)VC * (4 + 2 * S) * l2pad_size(K)) + 16;
+    return sizeof(float) * ((size_t)(1 + S) * rows_staged * VC + (size_t)VC * (4 + 2 * S) * l2pad_size(K) + (size_t)VC * 32 * (2 + S) * M) + 16;
 }
 
 template <int M, int S, int VC, int FIN, int MAXT>
@@ -204,7 +241,8 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
     const int rows_staged = g.nb * g.rb;
     float* stage = sm;                                            // [1+S][rows_staged][8]
     float* l2base = sm + (size_t)(1 + S) * rows_staged * VC;      // [8][SYS]
-    uint64_t* full = (uint64_t*)(l2base + (size_t)VC * SYS);
+    float* stash = l2base + (size_t)VC * SYS;                      // [(2+S)*M][32*VC]: level-2 warps park their level-1 state
+    uint64_t* full = (uint64_t*)(stash + (size_t)VC * 32 * (2 + S) * M);
     const int t = threadIdx.x, x = t % VC, k = t / VC, r0 = k * M;
     float* A = l2base + x * SYS; float* B = A + KP; float* Bd = B + KP; float* C = Bd + KP;
     float* F = C + KP; float* Fd = F + S * KP;
@@ -234,12 +272,21 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
         float aprev = 0.f;
         {
             const float* sw = stage + (size_t)r0 * VC + x;
+            if (live && r0 + M < a.h) {                                  // chunk strictly inside the column: no masks
 #pragma unroll
-            for (int m = 0; m < M; ++m) {
-                const bool in = live && (r0 + m < a.h);
-                c[m] = (live && (r0 + m < a.h - 1)) ? a.lam * sw[m * VC] : 0.f;                  // last row weight 0 (fgs_filter.cpp:658-660)
+                for (int m = 0; m < M; ++m) {
+                    c[m] = a.lam * sw[m * VC];
 #pragma unroll
-                for (int s = 0; s < S; ++s) f[s][m] = in ? sw[(size_t)(1 + s) * rows_staged * VC + m * VC] : 0.f;
+                    for (int s = 0; s < S; ++s) f[s][m] = sw[(size_t)(1 + s) * rows_staged * VC + m * VC];
+                }
+            } else {
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    const bool in = live && (r0 + m < a.h);
+                    c[m] = (live && (r0 + m < a.h - 1)) ? a.lam * sw[m * VC] : 0.f;              // last row weight 0 (fgs_filter.cpp:658-660)
+#pragma unroll
+                    for (int s = 0; s < S; ++s) f[s][m] = in ? sw[(size_t)(1 + s) * rows_staged * VC + m * VC] : 0.f;
+                }
             }
             if (live && k > 0 && r0 - 1 < a.h - 1) aprev = a.lam * sw[-VC];
         }
@@ -263,9 +310,25 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
         if (t == 0 && i + 1 < n_mine) issue(i + 1);
         {
             const int warp = t >> 5, nwarps = blockDim.x >> 5, lane = t & 31;
-            for (int sys = warp; sys < VC; sys += nwarps) {
-                float* A2 = l2base + sys * SYS;
-                level2_solve_warp<S>(A2, A2 + KP, A2 + 2 * KP, A2 + 3 * KP, A2 + 4 * KP, A2 + (4 + S) * KP, KP, M2, lane);
+            if (warp < VC) {
+                // the level-2 warps need their registers for the reduced systems: park the level-1 state meanwhile
+                const int ST = 32 * VC;
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    stash[m * ST + t] = c[m]; stash[(M + m) * ST + t] = v[m];
+#pragma unroll
+                    for (int s = 0; s < S; ++s) stash[((2 + s) * M + m) * ST + t] = f[s][m];
+                }
+                for (int sys = warp; sys < VC; sys += nwarps) {
+                    float* A2 = l2base + sys * SYS;
+                    level2_solve_warp<S>(A2, A2 + KP, A2 + 2 * KP, A2 + 3 * KP, A2 + 4 * KP, A2 + (4 + S) * KP, KP, M2, lane);
+                }
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    c[m] = stash[m * ST + t]; v[m] = stash[(M + m) * ST + t];
+#pragma unroll
+                    for (int s = 0; s < S; ++s) f[s][m] = stash[((2 + s) * M + m) * ST + t];
+                }
             }
         }
         __syncthreads();
@@ -275,19 +338,25 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
         __syncthreads();                       // level-2 scratch may be overwritten by the next strip from here on
         level1_fixup<M, S>(c, f, v, Uprev, Uown);
         if (live) {
-            const size_t off0 = (size_t)r0 * a.pitch + col;
+            const size_t off0 = (size_t)frame * a.p_frame + (size_t)r0 * a.pitch + col;
+            const int nrow = min(M, a.h - r0);                           // rows of this chunk inside the image (<= 0 for padding chunks)
             if (FIN == FIN_FLOAT) {
 #pragma unroll
-                for (int m = 0; m < M; ++m)
-                    if (r0 + m < a.h) {
+                for (int s = 0; s < S; ++s) {
+                    float* O = a.out[s] + off0;
+                    if (nrow == M) {
 #pragma unroll
-                        for (int s = 0; s < S; ++s) a.out[s][(size_t)frame * a.p_frame + off0 + (size_t)m * a.pitch] = f[s][m];
+                        for (int m = 0; m < M; ++m) O[m * a.pitch] = f[s][m];
+                    } else {
+#pragma unroll
+                        for (int m = 0; m < M; ++m) if (m < nrow) O[m * a.pitch] = f[s][m];
                     }
+                }
             } else {
                 int16_t* O = a.out16 + (size_t)frame * a.out16_frame + (size_t)r0 * a.out16_step + col;
 #pragma unroll
                 for (int m = 0; m < M; ++m)
-                    if (r0 + m < a.h) {
+                    if (m < nrow) {
                         const float val = (FIN == FIN_WLS) ? wls_normalise(f[0][m], f[S - 1][m]) : f[0][m];
                         O[(size_t)m * a.out16_step] = cvt_s16(val);
                     }
