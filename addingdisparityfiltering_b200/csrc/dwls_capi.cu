@@ -429,11 +429,15 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
         if (mask_only) { a.conf = nullptr; a.plane_dc = nullptr; a.plane_c = nullptr; }
         a.p_frame = L.plane; a.pitch = g.pitch;
         a.mask = mask; a.mask_step = mask_step;
-        const int tw = CF_T - 2 * a.radius;
-        const dim3 cgrid((g.rw + tw - 1) / tw, (g.rh + CF_ROWS - 1) / CF_ROWS, nf);
-        TIMED(K_CONF_R, st, conf_kernel<false><<<cgrid, CF_T, 0, st>>>(a));
+        const dim3 cgrid((g.rw + CF_TW - 1) / CF_TW, (g.rh + CF_ROWS - 1) / CF_ROWS, nf);
+        const size_t csmem = conf_smem_bytes(a.radius);
+        if (csmem > 48 * 1024) {
+            CK(cudaFuncSetAttribute(conf_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem));
+            CK(cudaFuncSetAttribute(conf_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem));
+        }
+        TIMED(K_CONF_R, st, conf_kernel<false><<<cgrid, CF_T, csmem, st>>>(a));
         CK(cudaGetLastError());
-        TIMED(K_CONF_L, st, conf_kernel<true><<<cgrid, CF_T, 0, st>>>(a));
+        TIMED(K_CONF_L, st, conf_kernel<true><<<cgrid, CF_T, csmem, st>>>(a));
         CK(cudaGetLastError());
         if (a.conf || a.mask) {          // zero the exported map (and the mask) outside the ROI (disparity_filters.cpp:187)
             BorderArgs ba;

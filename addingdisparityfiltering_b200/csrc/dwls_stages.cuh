@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "dwls_passes.cuh"
+#include "dwls_conf.cuh"
 
 namespace dwls {
 
@@ -83,131 +84,6 @@ __global__ void __launch_bounds__(WT_T) weights_kernel(const uint8_t* __restrict
     const size_t o = (size_t)frame * wframe + (size_t)i * pitch + j0;
     *(float4*)(chor + o) = make_float4(ho[0], ho[1], ho[2], ho[3]);
     *(float4*)(cvert + o) = make_float4(vo[0], vo[1], vo[2], vo[3]);
-}
-
-// ---------------------------------------------------------------------------------------------
-// confidence stage (disparity_filters.cpp:161-210, 306-341, 349-373)
-// ---------------------------------------------------------------------------------------------
-struct ConfArgs {
-    const int16_t* dl; int64_t dl_step, dl_frame;     // elements
-    const int16_t* dr; int64_t dr_step, dr_frame;
-    int dw, dh;                                       // disparity map size
-    int rx, ry, rw, rh;                               // valid_disp_ROI (228-233)
-    int rrx;                                          // mirrored right ROI x (202-203)
-    int radius;
-    float scale_f; double scale_d;                    // 1/k^2 as float (boxFilter) and double (sqrBoxFilter)
-    float roll_off;                                   // 0.001f / resize_factor^2 (359)
-    int thresh;                                       // (int)(resize_factor * LRC_thresh) (318)
-    float* conf_r; int64_t cr_frame; int cr_pitch;    // right discontinuity map, ROI-cropped workspace, 0..1
-    float* conf; int64_t conf_step, conf_frame;       // exported map (elements), full disparity size, 0..255; may be NULL
-    float* plane_dc; float* plane_c; int64_t p_frame; int pitch;   // ROI-cropped solver planes; NULL in half-res mode
-    uint8_t* mask; int64_t mask_step;                 // optional LRC decision export (frame 0 only)
-};
-
-__device__ __forceinline__ int reflect101(int p, int len)
-{
-    if (len == 1) return 0;
-    while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
-    return p;
-}
-
-constexpr int CF_T = 256;       // threads per CTA = tile columns including the 2*radius halo
-constexpr int CF_ROWS = 32;     // output rows per CTA
-constexpr int CF_PF = 4;        // rows fetched ahead per thread
-
-// Box variance by running sums, exact in integers: every thread owns one column of the ROI crop
-// (border = reflect-101 of the CROP, disparity_filters.cpp:168-174) and slides a (2r+1)-row window
-// down it (column sum, column sum of squares); the per-row column sums go through a double-buffered
-// shared row and each output thread adds its 2r+1 neighbours.  Then the exact rounding sequence of
-// boxFilter / sqrBoxFilter / ComputeDepthDisc_ParBody (349-373): int window sum * float(1/k^2);
-// exact sum of squares * double(1/k^2) -> float; unfused float ops.
-// grid = (ceil(rw / (CF_T - 2r)), ceil(rh / CF_ROWS), frames)
-// LEFT = false: right view, writes conf_r over the right ROI.
-// LEFT = true : left view + LRC (306-341) + *255 (209) + export + solver planes (286-290).
-template <bool LEFT>
-__global__ void __launch_bounds__(CF_T) conf_kernel(const ConfArgs a)
-{
-    __shared__ int cs_buf[2][CF_T];
-    __shared__ long long cq_buf[2][CF_T];
-    const int r = a.radius, tid = threadIdx.x, frame = blockIdx.z;
-    const int tw = CF_T - 2 * r;
-    const int cx = blockIdx.x * tw + tid - r;                      // crop column (halo threads fall outside [0, rw))
-    const int y0 = blockIdx.y * CF_ROWS, y1 = min(y0 + CF_ROWS, a.rh);
-    const int16_t* src = LEFT ? a.dl + (size_t)frame * a.dl_frame : a.dr + (size_t)frame * a.dr_frame;
-    const int64_t sstep = LEFT ? a.dl_step : a.dr_step;
-    const int16_t* col = src + (size_t)a.ry * sstep + (LEFT ? a.rx : a.rrx) + reflect101(cx, a.rw);
-    const bool is_out = tid >= r && tid < CF_T - r && cx < a.rw;
-
-    int cs = 0; long long cq = 0;
-    for (int d = -r; d < r; ++d) { const int v = col[(size_t)reflect101(y0 + d, a.rh) * sstep]; cs += v; cq += v * v; }
-    for (int yb = y0; yb < y1; yb += CF_PF) {
-        int vin[CF_PF], vout[CF_PF];
-#pragma unroll
-        for (int i = 0; i < CF_PF; ++i) {
-            vin[i] = col[(size_t)reflect101(yb + i + r, a.rh) * sstep];
-            vout[i] = col[(size_t)reflect101(yb + i - r, a.rh) * sstep];
-        }
-        float cv[CF_PF];
-#pragma unroll
-        for (int i = 0; i < CF_PF; ++i) {
-            cv[i] = 0.f;
-            if (yb + i >= y1) break;                                // uniform across the CTA
-            cs += vin[i]; cq += vin[i] * vin[i];
-            const int buf = i & 1;                                  // CF_PF is even, so this alternates across chunks too
-            cs_buf[buf][tid] = cs; cq_buf[buf][tid] = cq;
-            __syncthreads();
-            if (is_out) {
-                int s = 0; long long q = 0;
-                for (int d = -r; d <= r; ++d) { s += cs_buf[buf][tid + d]; q += cq_buf[buf][tid + d]; }
-                const float mean = __fmul_rn((float)s, a.scale_f);
-                const float meansq = (float)__dmul_rn((double)q, a.scale_d);
-                const float variance = __fsub_rn(meansq, __fmul_rn(mean, mean));
-                cv[i] = fmaxf(__fsub_rn(1.0f, __fmul_rn(a.roll_off, variance)), 0.0f);
-            }
-            cs -= vout[i]; cq -= vout[i] * vout[i];
-        }
-        if (!is_out) continue;
-        const int nrow = min(CF_PF, y1 - yb);
-        if (!LEFT) {
-#pragma unroll
-            for (int i = 0; i < CF_PF; ++i)
-                if (i < nrow) a.conf_r[(size_t)frame * a.cr_frame + (size_t)(yb + i) * a.cr_pitch + cx] = cv[i];
-        } else {
-            // left-right consistency for the CF_PF rows at once, so the dependent gathers of all rows are in flight together
-            const int gx = a.rx + cx;
-            int L[CF_PF], ridx[CF_PF], R[CF_PF];
-            float cr[CF_PF];
-            bool hit[CF_PF];
-#pragma unroll
-            for (int i = 0; i < CF_PF; ++i) L[i] = (i < nrow) ? col[(size_t)(yb + i) * sstep] : 0;
-#pragma unroll
-            for (int i = 0; i < CF_PF; ++i) {
-                ridx[i] = gx - (L[i] >> 4);                                                            // 331
-                hit[i] = i < nrow && ridx[i] >= a.rrx && ridx[i] < a.rrx + a.rw;                      // 332
-                R[i] = hit[i] ? a.dr[(size_t)frame * a.dr_frame + (size_t)(a.ry + yb + i) * a.dr_step + ridx[i]] : 0;
-                cr[i] = hit[i] ? a.conf_r[(size_t)frame * a.cr_frame + (size_t)(yb + i) * a.cr_pitch + (ridx[i] - a.rrx)] : 0.f;
-            }
-#pragma unroll
-            for (int i = 0; i < CF_PF; ++i) {
-                if (i >= nrow) break;
-                const int gy = a.ry + yb + i;
-                float cval = cv[i];
-                uint8_t m = 1;
-                if (hit[i]) {
-                    if (abs(L[i] + R[i]) < a.thresh) { cval = fminf(cval, cr[i]); m = 2; }              // 334-335
-                    else { cval = 0.0f; m = 3; }                                                        // 337
-                }
-                cval = __fmul_rn(255.0f, cval);                                                        // 209
-                if (a.mask && frame == 0) a.mask[(size_t)gy * a.mask_step + gx] = m;
-                if (a.plane_c) {
-                    const size_t po = (size_t)frame * a.p_frame + (size_t)(yb + i) * a.pitch + cx;
-                    a.plane_c[po] = cval;
-                    a.plane_dc[po] = __fmul_rn(cval, (float)L[i]);                                     // 289-290
-                }
-                if (a.conf) a.conf[(size_t)frame * a.conf_frame + (size_t)gy * a.conf_step + gx] = cval;
-            }
-        }
-    }
 }
 
 // everything outside the ROI: filtered output = 16*(min_disp-1) with min_disp forced to 0
