@@ -338,6 +338,78 @@ static dwls_status launch_border(dwls_ctx* ctx, const BorderArgs& ba, int frames
     return DWLS_OK;
 }
 
+// int16 disparity maps of a launch group as one 3-D tensor {cols, rows, frames} with a {256 x box_rows x 1} box;
+// returns false when the layout does not meet the TMA alignment rules (the caller then uses the plain-load path)
+static bool make_tmap_s16(dwls_ctx* ctx, CUtensorMap* tm, const int16_t* base, int cols, int rows, int frames, int64_t step_elems,
+                          int64_t frame_elems, int box_rows)
+{
+    if (((uintptr_t)base & 15) || (step_elems & 7) || step_elems <= 0) return false;
+    if (frames > 1 && ((frame_elems & 7) || frame_elems <= 0)) return false;
+    if (!g_encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn || q != cudaDriverEntryPointSuccess) return false;
+        g_encode = (EncodeTiledFn)fn;
+    }
+    const cuuint64_t dims[3] = { (cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)frames };
+    const cuuint64_t strides[2] = { (cuuint64_t)step_elems * 2, (cuuint64_t)(frames > 1 ? frame_elems : step_elems * rows) * 2 };
+    const cuuint32_t box[3] = { 256, (cuuint32_t)box_rows, 1 };
+    const cuuint32_t estr[3] = { 1, 1, 1 };
+    return g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// confidence stage: right view first (its map is gathered by the left view's LRC step)
+template <int R>
+static void launch_conf_run(const ConfArgs& a, int G, dim3 grid, cudaStream_t st, bool left, const CUtensorMap* tm)
+{
+    CUtensorMap none;
+    memset(&none, 0, sizeof none);
+    if (left) { if (tm) conf_run_kernel<R, true, true><<<grid, CR_T, 0, st>>>(a, G, *tm); else conf_run_kernel<R, true, false><<<grid, CR_T, 0, st>>>(a, G, none); }
+    else { if (tm) conf_run_kernel<R, false, true><<<grid, CR_T, 0, st>>>(a, G, *tm); else conf_run_kernel<R, false, false><<<grid, CR_T, 0, st>>>(a, G, none); }
+}
+
+static dwls_status launch_conf(dwls_ctx* ctx, const ConfArgs& a, int frames, cudaStream_t st)
+{
+    if (a.radius <= CR_MAXR) {
+        const int runs = (a.rw + 7) / 8, gmax = CR_GMAX;
+        const int tiles = (runs + gmax - 1) / gmax, G = (runs + tiles - 1) / tiles;
+        const dim3 grid(tiles, (a.rh + CR_TH - 1) / CR_TH, frames);
+        const int box_rows = CR_TH + 2 * a.radius + 1;
+        for (int left = 0; left < 2; ++left) {
+            CUtensorMap tm;
+            const bool tma = left ? make_tmap_s16(ctx, &tm, a.dl, a.dw, a.dh, frames, a.dl_step, a.dl_frame, box_rows)
+                                  : make_tmap_s16(ctx, &tm, a.dr, a.dw, a.dh, frames, a.dr_step, a.dr_frame, box_rows);
+            const CUtensorMap* ptm = tma ? &tm : nullptr;
+            KTimer kt_(ctx, left ? K_CONF_L : K_CONF_R, st);
+            switch (a.radius) {
+            case 0: launch_conf_run<0>(a, G, grid, st, left, ptm); break;
+            case 1: launch_conf_run<1>(a, G, grid, st, left, ptm); break;
+            case 2: launch_conf_run<2>(a, G, grid, st, left, ptm); break;
+            case 3: launch_conf_run<3>(a, G, grid, st, left, ptm); break;
+            case 4: launch_conf_run<4>(a, G, grid, st, left, ptm); break;
+            case 5: launch_conf_run<5>(a, G, grid, st, left, ptm); break;
+            case 6: launch_conf_run<6>(a, G, grid, st, left, ptm); break;
+            case 7: launch_conf_run<7>(a, G, grid, st, left, ptm); break;
+            default: launch_conf_run<8>(a, G, grid, st, left, ptm); break;
+            }
+            CK(cudaGetLastError());
+        }
+        return DWLS_OK;
+    }
+    const dim3 cgrid((a.rw + CF_TW - 1) / CF_TW, (a.rh + CF_ROWS - 1) / CF_ROWS, frames);
+    const size_t csmem = conf_smem_bytes(a.radius);
+    if (csmem > 48 * 1024) {
+        CK(cudaFuncSetAttribute(conf_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem));
+        CK(cudaFuncSetAttribute(conf_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem));
+    }
+    TIMED(K_CONF_R, st, conf_kernel<false><<<cgrid, CF_T, csmem, st>>>(a));
+    CK(cudaGetLastError());
+    TIMED(K_CONF_L, st, conf_kernel<true><<<cgrid, CF_T, csmem, st>>>(a));
+    CK(cudaGetLastError());
+    return DWLS_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // DisparityWLSFilter::filter on device buffers
 // ---------------------------------------------------------------------------------------------
@@ -389,7 +461,7 @@ static WsLayout ws_layout(const Geom& g, bool use_conf)
 {
     WsLayout l;
     l.plane = (size_t)g.pitch * g.fh;
-    l.cr_pitch = round_up(g.rw, 4);
+    l.cr_pitch = round_up(g.rw, 8);
     l.confr = use_conf ? (size_t)l.cr_pitch * g.rh : 0;
     l.conflo = (use_conf && !g.same) ? (size_t)g.dw * g.dh : 0;
     l.per_frame = 4 * l.plane + l.confr + l.conflo;
@@ -413,6 +485,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
     float* cexp = b->conf ? (float*)((uint8_t*)b->conf + (size_t)f0 * b->conf_frame) : nullptr;
 
     if (conf) {
+        dwls_status s2;
         ConfArgs a;
         memset(&a, 0, sizeof a);
         a.dl = dl; a.dl_step = b->dl_step / 2; a.dl_frame = b->dl_frame / 2;
@@ -429,16 +502,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
         if (mask_only) { a.conf = nullptr; a.plane_dc = nullptr; a.plane_c = nullptr; }
         a.p_frame = L.plane; a.pitch = g.pitch;
         a.mask = mask; a.mask_step = mask_step;
-        const dim3 cgrid((g.rw + CF_TW - 1) / CF_TW, (g.rh + CF_ROWS - 1) / CF_ROWS, nf);
-        const size_t csmem = conf_smem_bytes(a.radius);
-        if (csmem > 48 * 1024) {
-            CK(cudaFuncSetAttribute(conf_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem));
-            CK(cudaFuncSetAttribute(conf_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem));
-        }
-        TIMED(K_CONF_R, st, conf_kernel<false><<<cgrid, CF_T, csmem, st>>>(a));
-        CK(cudaGetLastError());
-        TIMED(K_CONF_L, st, conf_kernel<true><<<cgrid, CF_T, csmem, st>>>(a));
-        CK(cudaGetLastError());
+        if ((s2 = launch_conf(ctx, a, nf, st))) return s2;
         if (a.conf || a.mask) {          // zero the exported map (and the mask) outside the ROI (disparity_filters.cpp:187)
             BorderArgs ba;
             memset(&ba, 0, sizeof ba);
@@ -489,11 +553,14 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
 static int pick_group(const dwls_ctx* ctx, size_t per_frame_bytes, int n)
 {
     if (ctx->group_frames > 0) return ctx->group_frames < n ? ctx->group_frames : n;
-    // default: keep a group's workspace near 1 GiB so launches are large but allocation stays modest
-    size_t g = ((size_t)1 << 30) / (per_frame_bytes ? per_frame_bytes : 1);
+    // default: keep a group's workspace under 2 GiB so launches are large but allocation stays modest,
+    // and split the batch into groups of EQUAL size (a short trailing group is a launch too small to fill the GPU)
+    size_t g = ((size_t)2 << 30) / (per_frame_bytes ? per_frame_bytes : 1);
     if (g < 1) g = 1;
-    if (g > 32) g = 32;
-    return (int)(g < (size_t)n ? g : (size_t)n);
+    if (g > 48) g = 48;
+    if (g >= (size_t)n) return n;
+    const int groups = (n + (int)g - 1) / (int)g;
+    return (n + groups - 1) / groups;
 }
 
 static dwls_status validate_batch(dwls_ctx* ctx, const dwls_batch* b, const dwls_params* p)

@@ -6,6 +6,7 @@
 #include <stdint.h>
 #include "dwls_passes.cuh"
 #include "dwls_conf.cuh"
+#include "dwls_conf_run.cuh"
 
 namespace dwls {
 

@@ -164,6 +164,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--gather", action="store_true", help="all_gather the outputs over NCCL inside the timed region")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (tuning runs only)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -274,13 +275,15 @@ def main():
                 "kernels": {k: {"launches": n, "total_ms": round(t, 4), "share": round(t / sum(v[1] for v in ktimes.values()), 4)}
                             for k, (n, t) in ktimes.items()}}
     # ---- CPU baseline: the oracle on a bounded sample, all host threads ----
-    from oracle import oracle as O
-    threads = O.hardware_threads()
-    fps1 = cpu_frames_per_sec(base, 1, threads)
-    n_cpu = int(max(2, min(64, args.cpu_seconds * fps1)))
-    fps = cpu_frames_per_sec(base, n_cpu, threads)
-    cpu = {"value": fps * W * H / 1e6, "unit": "Mpix/s", "cores": threads, "kind": cpu_kind(),
-           "sample": "%d frames of the same 1080p workload, reference CPU code on all host threads" % n_cpu}
+    cpu = None
+    if not args.no_cpu:
+        from oracle import oracle as O
+        threads = O.hardware_threads()
+        fps1 = cpu_frames_per_sec(base, 1, threads)
+        n_cpu = int(max(2, min(64, args.cpu_seconds * fps1)))
+        fps = cpu_frames_per_sec(base, n_cpu, threads)
+        cpu = {"value": fps * W * H / 1e6, "unit": "Mpix/s", "cores": threads, "kind": cpu_kind(),
+               "sample": "%d frames of the same 1080p workload, reference CPU code on all host threads" % n_cpu}
     print(json.dumps({
         "metric": METRIC, "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
