@@ -390,8 +390,7 @@ static dwls_status launch_conf(dwls_ctx* ctx, const ConfArgs& a, int frames, cud
             case 4: launch_conf_run<4>(a, G, grid, st, left, ptm); break;
             case 5: launch_conf_run<5>(a, G, grid, st, left, ptm); break;
             case 6: launch_conf_run<6>(a, G, grid, st, left, ptm); break;
-            case 7: launch_conf_run<7>(a, G, grid, st, left, ptm); break;
-            default: launch_conf_run<8>(a, G, grid, st, left, ptm); break;
+            default: launch_conf_run<7>(a, G, grid, st, left, ptm); break;
             }
             CK(cudaGetLastError());
         }

@@ -1,4 +1,4 @@
-// dwls_conf_run.cuh — confidence stage for small discontinuity radii (R <= 8), the common case
+// dwls_conf_run.cuh — confidence stage for small discontinuity radii (R <= 7), the common case
 // (createDisparityWLSFilter derives R = ceil(0.33 * wsize) / ceil(0.5 * wsize),
 // disparity_filters.cpp:402,408).  Same arithmetic as dwls_conf.cuh (which remains the path for
 // larger radii): exact integer window sums, then the reference's rounding sequence
@@ -31,7 +31,7 @@ constexpr int CR_NB = 4;                   // row bands per CTA
 constexpr int CR_RB = 16;                  // rows per band
 constexpr int CR_TH = CR_NB * CR_RB;       // output rows per CTA
 constexpr int CR_T = 128;                  // threads per CTA (>= runs * CR_NB)
-constexpr int CR_MAXR = 8;
+constexpr int CR_MAXR = 7;                  // static shared memory (tile + gather buffers) stays under 48 KB
 
 constexpr int CR_HL = 8;                   // tile column c holds crop column tx0 - CR_HL + c
 constexpr int CR_GMAX = 29;                // runs of 8 px per tile: 8*G + 2*CR_HL + 7 (TMA realignment slack) <= 256
@@ -177,19 +177,22 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
         __syncthreads();
     }
 
-    // ---- per-thread march ----
-    const int band = tid / G, g = tid - band * G;
+    // ---- per-thread march: warp = band of CR_RB rows, lane = run of 8 columns ----
+    const int band = tid >> 5, g = tid & 31;
     const int cx0 = tx0 + 8 * g;                               // first output column of the run (crop coordinates)
     const int yb = ty0 + band * CR_RB;
-    if (band >= CR_NB || cx0 >= a.rw || yb >= a.rh) return;
+    if (yb >= a.rh) return;                                    // warp-uniform
+    const bool active = g < G && cx0 < a.rw;                   // lanes without a run still serve the LRC gathers of their warp
+    if (!LEFT && !active) return;
     const int yend = min(yb + CR_RB, a.rh);
     const int nvalid = min(8, a.rw - cx0);
+    __shared__ __align__(16) float capbuf[LEFT ? CR_NB * 512 : 4];   // per warp: 256 right confidences | 256 words holding the right disparities
 
     int s[NCOL]; long long q[NCOL];
 #pragma unroll
     for (int c = 0; c < NCOL; ++c) { s[c] = 0; q[c] = 0; }
     // tile row of crop row y is y - ty0 + R + 1; warm-up: rows yb-R-1 .. yb+R-1 (the first of them is the row the first step removes)
-    const uint16_t* tp = tile + (size_t)(band * CR_RB) * PITCH + CR_HL + 8 * g;   // tile row (yb - R - 1), the run's 8 centre columns
+    const uint16_t* tp = tile + (size_t)(band * CR_RB) * PITCH + CR_HL + 8 * (active ? g : 0);   // tile row (yb - R - 1), the run's 8 centre columns
 #pragma unroll 1
     for (int k = 0; k < 2 * R + 1; ++k) {
         uint32_t w[NW];
@@ -199,24 +202,27 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
     }
 
     for (int y = yb; y < yend; ++y, tp += PITCH) {
-        // left view: start the data-dependent gathers of the LRC check (306-341) first, they land while the sums are formed
         const int gx0 = a.rx + cx0, gy = a.ry + y;
-        int L[8], Rv[8];
-        float cr[8];
-        bool hit[8];
+        // left view: the data-dependent gathers of the LRC check (306-341) are issued TRANSPOSED (lane l takes pixels
+        // l, l+32, .. of the warp's row segment, so a warp request touches neighbouring addresses) as 4-byte
+        // cp.async copies into the warp's shared buffer; they land while the sums are formed.
         if (LEFT) {
-            uint32_t wc[NW];
-            cr_load_row<NW>(wc, tp + (size_t)(R + 1) * PITCH);   // centre row y
+            const int16_t* crow16 = (const int16_t*)tile + (size_t)(y - ylo) * PITCH + CR_HL + g;
             const int16_t* drow = a.dr + (size_t)frame * a.dr_frame + (size_t)gy * a.dr_step + a.rrx;
             const float* crow = a.conf_r + (size_t)frame * a.cr_frame + (size_t)y * a.cr_pitch;
+            const int xr = a.rx + tx0 + g - a.rrx;
+            const uint32_t cb = smem_u32(capbuf + band * 512 + g);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                L[i] = cr_elem<NW>(wc, RA + i);
-                const int ro = gx0 + i - (L[i] >> 4) - a.rrx;                                      // 331, relative to the right ROI
-                hit[i] = (unsigned)ro < (unsigned)a.rw;                                            // 332 (columns past the crop are never stored)
-                Rv[i] = hit[i] ? (int)__ldg(drow + ro) : 0;
-                cr[i] = hit[i] ? __ldg(crow + ro) : 0.f;
+            for (int k = 0; k < 8; ++k) {
+                if (32 * k + g < 8 * G) {
+                    const int ro = xr + 32 * k - ((int)crow16[32 * k] >> 4);                       // 331, relative to the right ROI
+                    if ((unsigned)ro < (unsigned)a.rw) {                                           // 332
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(cb + 4 * (32 * k)), "l"(crow + ro) : "memory");
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(cb + 4 * (256 + 32 * k)), "l"((uintptr_t)(drow + ro) & ~(uintptr_t)3) : "memory");
+                    }
+                }
             }
+            asm volatile("cp.async.commit_group;" ::: "memory");
         }
         uint32_t win[NW], wout[NW];
         cr_load_row<NW>(wout, tp);                               // row y-R-1 leaves
@@ -250,21 +256,36 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
 #pragma unroll
                 for (int i = 0; i < 8; ++i) if (i < nvalid) O[i] = cv[i];
         } else {
-            float dc[8];
-            uint8_t m[8];
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            __syncwarp();
+            if (active) {
+                const float* cb = capbuf + band * 512 + 8 * g;
+                const float4 c0 = *(const float4*)cb, c1 = *(const float4*)(cb + 4);
+                const uint4 r0 = *(const uint4*)(cb + 256), r1 = *(const uint4*)(cb + 260);
+                const float crv[8] = { c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w };
+                const uint32_t rw[8] = { r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w };
+                uint32_t wc[NW];
+                cr_load_row<NW>(wc, tp + (size_t)(R + 1) * PITCH);   // centre row y
+                const int16_t* drow = a.dr + (size_t)frame * a.dr_frame + (size_t)gy * a.dr_step + a.rrx;
+                const int xr = gx0 - a.rrx;
+                float dc[8];
+                uint8_t m[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                m[i] = 1;
-                if (hit[i]) {
-                    if (abs(L[i] + Rv[i]) < a.thresh) { cv[i] = fminf(cv[i], cr[i]); m[i] = 2; }   // 334-335
-                    else { cv[i] = 0.0f; m[i] = 3; }                                                // 337
+                for (int i = 0; i < 8; ++i) {
+                    const int L = cr_elem<NW>(wc, RA + i);
+                    const int ro = xr + i - (L >> 4);                                              // 331
+                    m[i] = 1;
+                    if ((unsigned)ro < (unsigned)a.rw) {                                           // 332
+                        const int Rv = ((uintptr_t)(drow + ro) & 2) ? ((int)rw[i] >> 16) : (int)(short)(rw[i] & 0xffffu);
+                        if (abs(L + Rv) < a.thresh) { cv[i] = fminf(cv[i], crv[i]); m[i] = 2; }    // 334-335
+                        else { cv[i] = 0.0f; m[i] = 3; }                                           // 337
+                    }
+                    cv[i] = __fmul_rn(255.0f, cv[i]);                                              // 209
+                    dc[i] = __fmul_rn(cv[i], (float)L);                                            // 289-290
                 }
-                cv[i] = __fmul_rn(255.0f, cv[i]);                                                  // 209
-                dc[i] = __fmul_rn(cv[i], (float)L[i]);                                             // 289-290
-            }
-            if (a.mask && frame == 0)
+                if (a.mask && frame == 0)
 #pragma unroll
-                for (int i = 0; i < 8; ++i) if (i < nvalid) a.mask[(size_t)gy * a.mask_step + gx0 + i] = m[i];
+                    for (int i = 0; i < 8; ++i) if (i < nvalid) a.mask[(size_t)gy * a.mask_step + gx0 + i] = m[i];
             if (a.plane_c) {
                 float* PC = a.plane_c + (size_t)frame * a.p_frame + (size_t)y * a.pitch + cx0;
                 float* PD = a.plane_dc + (size_t)frame * a.p_frame + (size_t)y * a.pitch + cx0;
@@ -283,6 +304,8 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
 #pragma unroll
                     for (int i = 0; i < 8; ++i) if (i < nvalid) E[i] = cv[i];
             }
+            }
+            __syncwarp();                          // the buffer is rewritten by the next row's copies
         }
     }
 }
