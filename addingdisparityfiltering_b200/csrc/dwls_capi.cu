@@ -317,10 +317,15 @@ static dwls_status run_sweeps(dwls_ctx* ctx, SolveArgs a, const float* chor, con
 static dwls_status launch_weights(dwls_ctx* ctx, const uint8_t* guide, int64_t gstep, int64_t gframe, int cn, int w, int h,
                                   int pitch, float* chor, float* cvert, int64_t wframe, int frames, cudaStream_t st)
 {
-    dim3 grid((pitch + WT_PX - 1) / WT_PX, h, frames);
+    // threads per CTA: spread the row over equally wide tiles of at most 1024 pixels
+    const int tiles = (pitch + 1023) / 1024;
+    const int nt = round_up((pitch + 4 * tiles - 1) / (4 * tiles), 32);
+    const int rowpitch = weights_row_pitch(nt, cn);
+    const size_t smem = (size_t)(WT_RB + 1) * rowpitch + 8;
+    dim3 grid((pitch + 4 * nt - 1) / (4 * nt), (h + WT_RB - 1) / WT_RB, frames);
     KTimer kt_(ctx, K_WEIGHTS, st);
-    if (cn == 1) weights_kernel<1><<<grid, WT_T, 0, st>>>(guide, gstep, gframe, w, h, pitch, ctx->lut, chor, cvert, wframe);
-    else weights_kernel<3><<<grid, WT_T, 0, st>>>(guide, gstep, gframe, w, h, pitch, ctx->lut, chor, cvert, wframe);
+    if (cn == 1) weights_kernel<1><<<grid, nt, smem, st>>>(guide, gstep, gframe, w, h, pitch, rowpitch, ctx->lut, chor, cvert, wframe);
+    else weights_kernel<3><<<grid, nt, smem, st>>>(guide, gstep, gframe, w, h, pitch, rowpitch, ctx->lut, chor, cvert, wframe);
     CK(cudaGetLastError());
     return DWLS_OK;
 }

@@ -26,65 +26,100 @@ __global__ void lut_kernel(float* lut, int n, float sigma)
 
 // ---------------------------------------------------------------------------------------------
 // weight planes (fgs_filter.cpp:593-616 horizontal, 625-661 vertical), guide = ROI view of the
-// 8-bit image.  A CTA handles WT_PX pixels of one row: the bytes of rows i and i+1 are staged in
-// shared memory with aligned 128-bit loads (the ROI view starts at an arbitrary byte), each
-// thread then forms the squared colour distances of 4 consecutive pixels, gathers the LUT and
-// writes two float4.  Columns w..pitch-1 are zero-filled.
-// grid = (ceil(pitch / WT_PX), h, frames)
+// 8-bit image.  A CTA covers 4*blockDim.x columns x WT_RB rows.  The WT_RB+1 guide row segments
+// it needs are fetched by the TMA engine as 1-D bulk copies (each from the 16-byte boundary below
+// the segment, so any ROI offset and row step works; an aligned 16-byte chunk holding a valid
+// byte never leaves the allocation) onto one mbarrier.  Every thread then walks down the rows
+// with its 4 pixels (+ right neighbour) of the current row in registers: squared colour
+// distances by VABSDIFF4 + IDP.4A, two LUT gathers per pixel, two float4 stores per row.
+// Columns w..pitch-1 are zero-filled.  grid = (ceil(pitch / (4*blockDim.x)), ceil(h / WT_RB), frames)
+// dynamic smem = (WT_RB+1) * rowpitch + 8
 // ---------------------------------------------------------------------------------------------
-constexpr int WT_T = 256, WT_PX = 4 * WT_T;
+constexpr int WT_RB = 8;
+__host__ __device__ inline int weights_row_pitch(int nt, int cn) { return ((4 * nt + 1) * cn + 15 + 15) / 16 * 16 + 16; }
+
+// pixels 0..4 of a thread (channels in the low bytes, high bytes zero) from the staged row; off = byte offset of pixel 0
+template <int CN>
+__device__ __forceinline__ void wt_pixels(const uint8_t* row, int off, uint32_t (&P)[5])
+{
+    const uint32_t* wp = (const uint32_t*)(row + (off & ~3));
+    const int bs = (off & 3) * 8;
+    if (CN == 3) {
+        const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3], w4 = wp[4];
+        const uint32_t b0 = __funnelshift_r(w0, w1, bs), b1 = __funnelshift_r(w1, w2, bs), b2 = __funnelshift_r(w2, w3, bs),
+                       b3 = __funnelshift_r(w3, w4, bs);
+        P[0] = b0 & 0xffffffu;
+        P[1] = __funnelshift_r(b0, b1, 24) & 0xffffffu;
+        P[2] = __funnelshift_r(b1, b2, 16) & 0xffffffu;
+        P[3] = b2 >> 8;
+        P[4] = b3 & 0xffffffu;
+    } else {
+        const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
+        const uint32_t b0 = __funnelshift_r(w0, w1, bs), b1 = __funnelshift_r(w1, w2, bs);
+        P[0] = b0 & 0xffu; P[1] = (b0 >> 8) & 0xffu; P[2] = (b0 >> 16) & 0xffu; P[3] = b0 >> 24; P[4] = b1 & 0xffu;
+    }
+}
+__device__ __forceinline__ int wt_dist2(uint32_t a, uint32_t b)
+{
+    const uint32_t d = __vabsdiffu4(a, b);
+    return (int)__dp4a(d, d, 0u);
+}
 
 template <int CN>
-__global__ void __launch_bounds__(WT_T) weights_kernel(const uint8_t* __restrict__ guide, int64_t gstep, int64_t gframe,
-                                                       int w, int h, int pitch, const float* __restrict__ lut,
-                                                       float* __restrict__ chor, float* __restrict__ cvert, int64_t wframe)
+__global__ void __launch_bounds__(256) weights_kernel(const uint8_t* __restrict__ guide, int64_t gstep, int64_t gframe,
+                                                      int w, int h, int pitch, int rowpitch, const float* __restrict__ lut,
+                                                      float* __restrict__ chor, float* __restrict__ cvert, int64_t wframe)
 {
-    constexpr int ROWB = ((WT_PX + 1) * CN + 15 + 15) / 16 * 16;       // staged bytes per row incl. misalignment slack
-    __shared__ __align__(16) uint8_t sm[2][ROWB];
-    const int tid = threadIdx.x, i = blockIdx.y, frame = blockIdx.z, c0 = blockIdx.x * WT_PX;
-    const int npx = min(WT_PX + 1, w - c0);                             // pixels available from c0 on (incl. the right neighbour)
-    int mis[2] = { 0, 0 };
-    if (npx > 0) {
-#pragma unroll
-        for (int rr = 0; rr < 2; ++rr) {
-            if (i + rr >= h) break;
-            const uint8_t* rp = guide + (size_t)frame * gframe + (size_t)(i + rr) * gstep + (size_t)c0 * CN;
-            mis[rr] = (int)((uintptr_t)rp & 15);
-            const uint4* base = (const uint4*)(rp - mis[rr]);           // an aligned 16-byte chunk holding >= 1 valid byte never crosses a page
-            const int nch = (mis[rr] + npx * CN + 15) >> 4;
-            for (int k = tid; k < nch; k += WT_T) ((uint4*)sm[rr])[k] = __ldg(base + k);
-        }
-    }
+    extern __shared__ __align__(128) uint8_t wsm[];
+    uint64_t* bar = (uint64_t*)(wsm + (size_t)(WT_RB + 1) * rowpitch);
+    const int tid = threadIdx.x, frame = blockIdx.z, c0 = blockIdx.x * 4 * blockDim.x, i0 = blockIdx.y * WT_RB;
+    const int nrows = min(WT_RB + 1, h - i0);                           // guide rows staged
+    const int npx = min(4 * (int)blockDim.x + 1, w - c0);               // pixels available from c0 on (incl. the right neighbour)
+    const uint8_t* seg0 = guide + (size_t)frame * gframe + (size_t)i0 * gstep + (size_t)c0 * CN;
+    if (tid == 0) { mbar_init(bar, npx > 0 ? nrows : 1); mbar_fence_init(); }
     __syncthreads();
+    if (npx > 0) {
+        if (tid < nrows) {
+            const uint8_t* rp = seg0 + (size_t)tid * gstep;
+            const int mis = (int)((uintptr_t)rp & 15);
+            const uint32_t bytes = (uint32_t)((mis + npx * CN + 15) & ~15);
+            mbar_arrive_expect_tx(bar, bytes);
+            bulk_g2s(wsm + (size_t)tid * rowpitch, rp - mis, bytes, bar);
+        }
+        mbar_wait(bar, 0);
+    }
     const int j0 = c0 + 4 * tid;
     if (j0 >= pitch) return;
-    float ho[4] = { 0.f, 0.f, 0.f, 0.f }, vo[4] = { 0.f, 0.f, 0.f, 0.f };
-    if (j0 < w) {
-        const uint8_t* r0 = sm[0] + mis[0] + 4 * tid * CN;
-        const uint8_t* r1 = sm[1] + mis[1] + 4 * tid * CN;
-        const bool vr = i + 1 < h;
-        int px[5][CN];
+    const int rows_out = min(WT_RB, h - i0);
+    float* oh = chor + (size_t)frame * wframe + (size_t)i0 * pitch + j0;
+    float* ov = cvert + (size_t)frame * wframe + (size_t)i0 * pitch + j0;
+    if (j0 >= w) {
+        for (int r = 0; r < rows_out; ++r) {
+            *(float4*)(oh + (size_t)r * pitch) = make_float4(0.f, 0.f, 0.f, 0.f);
+            *(float4*)(ov + (size_t)r * pitch) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        return;
+    }
+    const int nh = min(4, w - 1 - j0), nv = min(4, w - j0);             // pixels of the run with a right neighbour / inside the image
+    uint32_t P[5], N[5];
+    wt_pixels<CN>(wsm, (int)((uintptr_t)seg0 & 15) + 4 * tid * CN, P);
 #pragma unroll
-        for (int q = 0; q < 5; ++q)
-#pragma unroll
-            for (int ch = 0; ch < CN; ++ch) px[q][ch] = (j0 + q < w) ? r0[q * CN + ch] : 0;
+    for (int q = 0; q < 5; ++q) N[q] = 0;
+#pragma unroll 2
+    for (int r = 0; r < rows_out; ++r) {
+        const bool vr = i0 + r + 1 < h;                                  // Cvert[h-1][j] = 0 (658-660)
+        if (vr) wt_pixels<CN>(wsm + (size_t)(r + 1) * rowpitch, (int)((uintptr_t)(seg0 + (size_t)(r + 1) * gstep) & 15) + 4 * tid * CN, N);
+        float ho[4], vo[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            if (j0 + q >= w) break;
-            int dh = 0, dv = 0;
-#pragma unroll
-            for (int ch = 0; ch < CN; ++ch) {
-                const int t = px[q][ch] - px[q + 1][ch];
-                dh += t * t;
-                if (vr) { const int u = px[q][ch] - (int)r1[q * CN + ch]; dv += u * u; }
-            }
-            ho[q] = (j0 + q + 1 < w) ? __ldg(lut + dh) : 0.f;           // Chor[i][w-1] = 0 (614)
-            vo[q] = vr ? __ldg(lut + dv) : 0.f;                          // Cvert[h-1][j] = 0 (658-660)
+            ho[q] = (q < nh) ? __ldg(lut + wt_dist2(P[q], P[q + 1])) : 0.f;   // Chor[i][w-1] = 0 (614)
+            vo[q] = (vr && q < nv) ? __ldg(lut + wt_dist2(P[q], N[q])) : 0.f;
         }
+        *(float4*)(oh + (size_t)r * pitch) = make_float4(ho[0], ho[1], ho[2], ho[3]);
+        *(float4*)(ov + (size_t)r * pitch) = make_float4(vo[0], vo[1], vo[2], vo[3]);
+#pragma unroll
+        for (int q = 0; q < 5; ++q) P[q] = N[q];
     }
-    const size_t o = (size_t)frame * wframe + (size_t)i * pitch + j0;
-    *(float4*)(chor + o) = make_float4(ho[0], ho[1], ho[2], ho[3]);
-    *(float4*)(cvert + o) = make_float4(vo[0], vo[1], vo[2], vo[3]);
 }
 
 // everything outside the ROI: filtered output = 16*(min_disp-1) with min_disp forced to 0
