@@ -276,7 +276,10 @@ static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
     if ((s = make_tmap(ctx, &t0, a.in[0], a.pitch, rows, VC, g.rb))) return s;
     if (S > 1) { if ((s = make_tmap(ctx, &t1, a.in[1], a.pitch, rows, VC, g.rb))) return s; }
     else t1 = t0;
-    int grid = ctx->num_sms;
+    int per_sm = 1;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, VC * pl.vK, smem));
+    if (per_sm < 1) return fail(ctx, DWLS_CUDA_ERROR, "column pass does not fit on an SM");
+    int grid = ctx->num_sms * per_sm;
     if (grid > g.strips_total) grid = g.strips_total;
     TIMED(FIN == FIN_FLOAT ? K_VSOLVE : K_VSOLVE_FIN, st, k<<<grid, VC * pl.vK, smem, st>>>(a, g, tw, t0, t1));
     CK(cudaGetLastError());
@@ -286,6 +289,8 @@ static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
 template <int S, int FIN>
 static dwls_status launch_v(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
+    static const int vc4 = getenv("DWLS_VC4") ? atoi(getenv("DWLS_VC4")) : 0;
+    if (pl.vM == 9 && vc4) return launch_v_inst<9, S, 4, FIN, 512>(ctx, a, pl, frames, st);
     if (pl.vM == 9) return launch_v_inst<9, S, 8, FIN, 1024>(ctx, a, pl, frames, st);
     if (pl.vCols == 4) return launch_v_inst<17, S, 4, FIN, 512>(ctx, a, pl, frames, st);
     return fail(ctx, DWLS_UNSUPPORTED, "column pass supports at most 2176 rows");
@@ -332,14 +337,13 @@ static dwls_status launch_weights(dwls_ctx* ctx, const uint8_t* guide, int64_t g
 
 static dwls_status launch_border(dwls_ctx* ctx, const BorderArgs& ba, int frames, cudaStream_t st)
 {
-    if (ba.W > ba.rw) {
-        TIMED(K_FILL, st, border_kernel<true><<<dim3((ba.W - ba.rw + 255) / 256, ba.rh, frames), 256, 0, st>>>(ba));
-        CK(cudaGetLastError());
-    }
-    if (ba.H > ba.rh) {
-        TIMED(K_FILL, st, border_kernel<false><<<dim3((ba.W + 255) / 256, ba.H - ba.rh, frames), 256, 0, st>>>(ba));
-        CK(cudaGetLastError());
-    }
+    const int tasks = (ba.H - ba.rh) + (ba.W > ba.rw ? ba.rh : 0);       // rows of the bands, one warp each
+    if (tasks <= 0) return DWLS_OK;
+    int blocks = (tasks + 7) / 8;
+    const int cap = (ctx->num_sms * 8 + frames - 1) / frames;
+    if (blocks > cap) blocks = cap < 1 ? 1 : cap;
+    TIMED(K_FILL, st, border_kernel<<<dim3(blocks, frames), 256, 0, st>>>(ba));
+    CK(cudaGetLastError());
     return DWLS_OK;
 }
 
@@ -488,6 +492,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
     int16_t* out = b->out ? (int16_t*)((uint8_t*)b->out + (size_t)f0 * b->out_frame) : nullptr;
     float* cexp = b->conf ? (float*)((uint8_t*)b->conf + (size_t)f0 * b->conf_frame) : nullptr;
 
+    bool out_border_done = false;
     if (conf) {
         dwls_status s2;
         ConfArgs a;
@@ -512,6 +517,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
             memset(&ba, 0, sizeof ba);
             ba.conf = a.conf; ba.conf_step = a.conf_step; ba.conf_frame = a.conf_frame; ba.mask = a.mask; ba.mask_step = a.mask_step;
             ba.W = g.dw; ba.H = g.dh; ba.rx = g.rx; ba.ry = g.ry; ba.rw = g.rw; ba.rh = g.rh;
+            if (g.same && !mask_only) { ba.out = out; ba.out_step = b->out_step / 2; ba.out_frame = b->out_frame / 2; out_border_done = true; }
             dwls_status bs = launch_border(ctx, ba, nf, st);
             if (bs) return bs;
         }
@@ -535,7 +541,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
                                                                             b->dl_frame / 2, g.fw, g.fh, p0, L.plane, g.pitch));
         CK(cudaGetLastError());
     }
-    {
+    if (!out_border_done) {
         BorderArgs ba;
         memset(&ba, 0, sizeof ba);
         ba.out = out; ba.out_step = b->out_step / 2; ba.out_frame = b->out_frame / 2;

@@ -36,9 +36,9 @@ enum { FIN_FLOAT = 0, FIN_WLS = 1, FIN_S16 = 2 };
 // OpenCV saturate_cast<short>(float): cvRound (ties-to-even; NaN / |v|>=2^31 -> INT_MIN) then clamp
 __device__ __forceinline__ int16_t cvt_s16(float v)
 {
-    if (!(fabsf(v) < 2147483648.0f)) return (int16_t)-32768;
-    int i = __float2int_rn(v);
-    return (int16_t)max(-32768, min(32767, i));
+    short r;
+    asm("cvt.rni.sat.s16.f32 %0, %1;" : "=h"(r) : "f"(v));
+    return (fabsf(v) < 2147483648.0f) ? (int16_t)r : (int16_t)-32768;
 }
 __device__ __forceinline__ uint8_t cvt_u8(float v)
 {
@@ -50,7 +50,16 @@ __device__ __forceinline__ uint8_t cvt_u8(float v)
 __device__ __forceinline__ float wls_normalise(float dc, float c)
 {
     const float den = __fadd_rn(fmaxf(c, 0.0f), __int_as_float(71));   // 71 * 2^-149 == 1e-43f
-    const float rec = __fdiv_rn(1.0f, den);
+    float rec;
+    if (den >= 1.1754944e-38f && den <= 8.0e37f) {
+        // den and 1/den are normal numbers: MUFU.RCP and one Newton step give the correctly rounded reciprocal
+        // (up to ties 2^-22 apart), which is what the reference's IEEE division returns
+        float r;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(den));
+        rec = fmaf(r, fmaf(-den, r, 1.0f), r);
+    } else {
+        rec = __fdiv_rn(1.0f, den);
+    }
     return __fmul_rn(dc, rec);
 }
 

@@ -124,30 +124,36 @@ __global__ void __launch_bounds__(256) weights_kernel(const uint8_t* __restrict_
 
 // everything outside the ROI: filtered output = 16*(min_disp-1) with min_disp forced to 0
 // (disparity_filters.cpp:149,254,284) and, when exported, confidence = 0 (187) / mask = 0.
-// Two launches cover only the border: side bands (rows of the ROI, columns outside it) and the
-// top/bottom bands (full rows).  grid = (ceil(cols/256), rows, frames)
+// One launch covers only the border: top/bottom bands (full rows) and side bands (rows of the ROI,
+// columns outside it).
 struct BorderArgs {
     int16_t* out; int64_t out_step, out_frame;       // elements; may be NULL
     float* conf; int64_t conf_step, conf_frame;      // elements; may be NULL
     uint8_t* mask; int64_t mask_step;                // may be NULL (frame 0 only)
     int W, H, rx, ry, rw, rh;
 };
-template <bool SIDES>
+// grid = (blocks, frames); a warp takes one row of a band at a time, its lanes stride over the columns
 __global__ void __launch_bounds__(256) border_kernel(const BorderArgs a)
 {
-    int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
-    const int frame = blockIdx.z;
-    if (SIDES) {
-        if (j >= a.W - a.rw) return;
-        if (j >= a.rx) j += a.rw;
-        i += a.ry;
-    } else {
-        if (j >= a.W) return;
-        if (i >= a.ry) i += a.rh;
+    const int full_rows = a.H - a.rh, side_cols = a.W - a.rw;
+    const int tasks = full_rows + (side_cols > 0 ? a.rh : 0);
+    const int frame = blockIdx.y, lane = threadIdx.x & 31;
+    const int warps = gridDim.x * (blockDim.x >> 5);
+    for (int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); t < tasks; t += warps) {
+        const bool side = t >= full_rows;
+        int i = side ? a.ry + (t - full_rows) : t;
+        if (!side && i >= a.ry) i += a.rh;
+        const int n = side ? side_cols : a.W;
+        int16_t* o = a.out ? a.out + (size_t)frame * a.out_frame + (size_t)i * a.out_step : nullptr;
+        float* c = a.conf ? a.conf + (size_t)frame * a.conf_frame + (size_t)i * a.conf_step : nullptr;
+        uint8_t* m = (a.mask && frame == 0) ? a.mask + (size_t)i * a.mask_step : nullptr;
+        for (int k = lane; k < n; k += 32) {
+            const int j = (side && k >= a.rx) ? k + a.rw : k;
+            if (o) o[j] = (int16_t)-16;
+            if (c) c[j] = 0.f;
+            if (m) m[j] = 0;
+        }
     }
-    if (a.out) a.out[(size_t)frame * a.out_frame + (size_t)i * a.out_step + j] = (int16_t)-16;
-    if (a.conf) a.conf[(size_t)frame * a.conf_frame + (size_t)i * a.conf_step + j] = 0.f;
-    if (a.mask && frame == 0) a.mask[(size_t)i * a.mask_step + j] = 0;
 }
 
 // ---------------------------------------------------------------------------------------------
