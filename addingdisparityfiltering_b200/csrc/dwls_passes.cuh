@@ -33,6 +33,12 @@ struct SolveArgs {
 
 enum { FIN_FLOAT = 0, FIN_WLS = 1, FIN_S16 = 2 };
 
+// 256-bit global store (sm_100: STG.256), p 32-byte aligned
+__device__ __forceinline__ void st_global_v8(float* p, float a, float b, float c, float d, float e, float f, float g, float h)
+{
+    asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d), "f"(e), "f"(f), "f"(g), "f"(h) : "memory");
+}
+
 // OpenCV saturate_cast<short>(float): cvRound (ties-to-even; NaN / |v|>=2^31 -> INT_MIN) then clamp
 __device__ __forceinline__ int16_t cvt_s16(float v)
 {
@@ -208,8 +214,12 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? HMINB : 1)) hsolve_kernel
 #pragma unroll
             for (int s = 0; s < S; ++s) {
                 float* P = a.out[s] + (size_t)frame * a.p_frame + (size_t)row * a.pitch + j0;
+                if (HM == 8) {
+                    st_global_v8(P, f[s][0], f[s][1], f[s][2], f[s][3], f[s][4], f[s][5], f[s][6], f[s][7]);     // one full 32-byte sector per thread
+                } else {
 #pragma unroll
-                for (int q = 0; q < HM / 4; ++q) *((float4*)P + q) = make_float4(f[s][4 * q], f[s][4 * q + 1], f[s][4 * q + 2], f[s][4 * q + 3]);
+                    for (int q = 0; q < HM / 4; ++q) *((float4*)P + q) = make_float4(f[s][4 * q], f[s][4 * q + 1], f[s][4 * q + 2], f[s][4 * q + 3]);
+                }
             }
         }
     }
