@@ -369,13 +369,22 @@ static bool make_tmap_s16(dwls_ctx* ctx, CUtensorMap* tm, const int16_t* base, i
 }
 
 // confidence stage: right view first (its map is gathered by the left view's LRC step)
+template <int R, bool LEFT, bool TMA>
+static void launch_conf_inst(const ConfArgs& a, int G, dim3 grid, cudaStream_t st, const CUtensorMap& tm)
+{
+    const size_t smem = conf_run_smem(R, LEFT);
+    static bool attr_set = false;
+    if (!attr_set) { cudaFuncSetAttribute(conf_run_kernel<R, LEFT, TMA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr_set = true; }
+    conf_run_kernel<R, LEFT, TMA><<<grid, CR_T, smem, st>>>(a, G, tm);
+}
+
 template <int R>
 static void launch_conf_run(const ConfArgs& a, int G, dim3 grid, cudaStream_t st, bool left, const CUtensorMap* tm)
 {
     CUtensorMap none;
     memset(&none, 0, sizeof none);
-    if (left) { if (tm) conf_run_kernel<R, true, true><<<grid, CR_T, 0, st>>>(a, G, *tm); else conf_run_kernel<R, true, false><<<grid, CR_T, 0, st>>>(a, G, none); }
-    else { if (tm) conf_run_kernel<R, false, true><<<grid, CR_T, 0, st>>>(a, G, *tm); else conf_run_kernel<R, false, false><<<grid, CR_T, 0, st>>>(a, G, none); }
+    if (left) { if (tm) launch_conf_inst<R, true, true>(a, G, grid, st, *tm); else launch_conf_inst<R, true, false>(a, G, grid, st, none); }
+    else { if (tm) launch_conf_inst<R, false, true>(a, G, grid, st, *tm); else launch_conf_inst<R, false, false>(a, G, grid, st, none); }
 }
 
 static dwls_status launch_conf(dwls_ctx* ctx, const ConfArgs& a, int frames, cudaStream_t st)

@@ -36,6 +36,9 @@ constexpr int CR_MAXR = 7;                  // static shared memory (tile + gath
 constexpr int CR_HL = 8;                   // tile column c holds crop column tx0 - CR_HL + c
 constexpr int CR_GMAX = 29;                // runs of 8 px per tile: 8*G + 2*CR_HL + 7 (TMA realignment slack) <= 256
 
+// dynamic shared memory of conf_run_kernel: tile, per warp 2 x (256 right confidences | 256 words holding right disparities), row table
+__host__ __device__ inline size_t conf_run_smem(int r, bool left) { return (size_t)(CR_TH + 2 * r + 1) * 512 + (left ? CR_NB * 2 * 512 * 4 : 0) + (CR_TH + 2 * r + 1) * 4 + 16; }
+
 template <int R>
 struct CrGeom {
     static constexpr int RA = (R + 1) & ~1;                 // halo rounded up to even: whole 32-bit words
@@ -90,8 +93,10 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
 {
     using Gm = CrGeom<R>;
     constexpr int RA = Gm::RA, PITCH = Gm::PITCH, TR = Gm::TR, NW = Gm::NW, NCOL = Gm::NCOL, OFF = RA - R;
-    __shared__ __align__(128) uint16_t tile[TR * PITCH];
-    __shared__ int rowy[TR];
+    extern __shared__ __align__(128) unsigned char cr_smem[];   // tile | gather buffers (left view) | row table (plain-load path)
+    uint16_t* tile = (uint16_t*)cr_smem;
+    float* capbuf = (float*)(cr_smem + (size_t)TR * PITCH * 2);
+    int* rowy = (int*)(capbuf + (LEFT ? CR_NB * 2 * 512 : 0));
     const int tid = threadIdx.x, frame = blockIdx.z;
     const int tx0 = blockIdx.x * 8 * G, ty0 = blockIdx.y * CR_TH;
     const int64_t sstep = LEFT ? a.dl_step : a.dr_step;
@@ -186,7 +191,6 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
     if (!LEFT && !active) return;
     const int yend = min(yb + CR_RB, a.rh);
     const int nvalid = min(8, a.rw - cx0);
-    __shared__ __align__(16) float capbuf[LEFT ? CR_NB * 512 : 4];   // per warp: 256 right confidences | 256 words holding the right disparities
 
     int s[NCOL]; long long q[NCOL];
 #pragma unroll
@@ -201,27 +205,34 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
         for (int c = 0; c < NCOL; ++c) { const int v = cr_elem<NW>(w, c + OFF); s[c] += v; q[c] += v * v; }
     }
 
+    // left view: the data-dependent gathers of the LRC check (306-341) are issued TRANSPOSED (lane l takes pixels
+    // l, l+32, .. of the warp's row segment, so a warp request touches neighbouring addresses) as 4-byte cp.async
+    // copies into the warp's shared buffer, one row ahead, and land while the sums of the current row are formed.
+    // Misses are issued with src-size 0 (zero fill, no global access) so the loop has no branches.
+    auto issue_gather = [&](int y, int buf) {
+        const int16_t* crow16 = (const int16_t*)tile + (size_t)(y - ylo) * PITCH + CR_HL + g;
+        const int16_t* drow = a.dr + (size_t)frame * a.dr_frame + (size_t)(a.ry + y) * a.dr_step + a.rrx;
+        const float* crow = a.conf_r + (size_t)frame * a.cr_frame + (size_t)y * a.cr_pitch;
+        const int xr = a.rx + tx0 + g - a.rrx;
+        const uint32_t cb = smem_u32(capbuf + (band * 2 + buf) * 512 + g);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const bool in = 32 * k + g < 8 * G;
+            const int L = in ? (int)crow16[32 * k] : 0;
+            const int ro = xr + 32 * k - (L >> 4);                                                 // 331, relative to the right ROI
+            const bool ok = in && (unsigned)ro < (unsigned)a.rw;                                   // 332
+            const int roc = ok ? ro : 0;
+            const uint32_t sz = ok ? 4u : 0u;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(cb + 4 * (32 * k)), "l"(crow + roc), "r"(sz) : "memory");
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(cb + 4 * (256 + 32 * k)), "l"((uintptr_t)(drow + roc) & ~(uintptr_t)3), "r"(sz) : "memory");
+        }
+    };
+    if (LEFT) { issue_gather(yb, 0); asm volatile("cp.async.commit_group;" ::: "memory"); }
+
     for (int y = yb; y < yend; ++y, tp += PITCH) {
         const int gx0 = a.rx + cx0, gy = a.ry + y;
-        // left view: the data-dependent gathers of the LRC check (306-341) are issued TRANSPOSED (lane l takes pixels
-        // l, l+32, .. of the warp's row segment, so a warp request touches neighbouring addresses) as 4-byte
-        // cp.async copies into the warp's shared buffer; they land while the sums are formed.
         if (LEFT) {
-            const int16_t* crow16 = (const int16_t*)tile + (size_t)(y - ylo) * PITCH + CR_HL + g;
-            const int16_t* drow = a.dr + (size_t)frame * a.dr_frame + (size_t)gy * a.dr_step + a.rrx;
-            const float* crow = a.conf_r + (size_t)frame * a.cr_frame + (size_t)y * a.cr_pitch;
-            const int xr = a.rx + tx0 + g - a.rrx;
-            const uint32_t cb = smem_u32(capbuf + band * 512 + g);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                if (32 * k + g < 8 * G) {
-                    const int ro = xr + 32 * k - ((int)crow16[32 * k] >> 4);                       // 331, relative to the right ROI
-                    if ((unsigned)ro < (unsigned)a.rw) {                                           // 332
-                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(cb + 4 * (32 * k)), "l"(crow + ro) : "memory");
-                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(cb + 4 * (256 + 32 * k)), "l"((uintptr_t)(drow + ro) & ~(uintptr_t)3) : "memory");
-                    }
-                }
-            }
+            if (y + 1 < yend) issue_gather(y + 1, (y + 1 - yb) & 1);
             asm volatile("cp.async.commit_group;" ::: "memory");
         }
         uint32_t win[NW], wout[NW];
@@ -256,31 +267,31 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
 #pragma unroll
                 for (int i = 0; i < 8; ++i) if (i < nvalid) O[i] = cv[i];
         } else {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            asm volatile("cp.async.wait_group 1;" ::: "memory");     // everything but the row just requested has landed
             __syncwarp();
             if (active) {
-                const float* cb = capbuf + band * 512 + 8 * g;
+                const float* cb = capbuf + (band * 2 + ((y - yb) & 1)) * 512 + 8 * g;
                 const float4 c0 = *(const float4*)cb, c1 = *(const float4*)(cb + 4);
                 const uint4 r0 = *(const uint4*)(cb + 256), r1 = *(const uint4*)(cb + 260);
                 const float crv[8] = { c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w };
-                const uint32_t rw[8] = { r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w };
+                const uint32_t rwd[8] = { r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w };
                 uint32_t wc[NW];
                 cr_load_row<NW>(wc, tp + (size_t)(R + 1) * PITCH);   // centre row y
                 const int16_t* drow = a.dr + (size_t)frame * a.dr_frame + (size_t)gy * a.dr_step + a.rrx;
                 const int xr = gx0 - a.rrx;
+                const int par0 = (int)(((uintptr_t)drow >> 1) & 1);  // which half of the fetched word holds element ro: (par0 + ro) & 1
                 float dc[8];
                 uint8_t m[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     const int L = cr_elem<NW>(wc, RA + i);
                     const int ro = xr + i - (L >> 4);                                              // 331
-                    m[i] = 1;
-                    if ((unsigned)ro < (unsigned)a.rw) {                                           // 332
-                        const int Rv = ((uintptr_t)(drow + ro) & 2) ? ((int)rw[i] >> 16) : (int)(short)(rw[i] & 0xffffu);
-                        if (abs(L + Rv) < a.thresh) { cv[i] = fminf(cv[i], crv[i]); m[i] = 2; }    // 334-335
-                        else { cv[i] = 0.0f; m[i] = 3; }                                           // 337
-                    }
-                    cv[i] = __fmul_rn(255.0f, cv[i]);                                              // 209
+                    const bool hit = (unsigned)ro < (unsigned)a.rw;                                // 332
+                    const int Rv = ((par0 + ro) & 1) ? ((int)rwd[i] >> 16) : (int)(short)(rwd[i] & 0xffffu);
+                    const bool cons = abs(L + Rv) < a.thresh;                                      // 334
+                    const float cap = hit ? (cons ? crv[i] : 0.0f) : __int_as_float(0x7f800000);   // min(confL, confR) / 0 / keep (335-337)
+                    m[i] = hit ? (cons ? 2 : 3) : 1;
+                    cv[i] = __fmul_rn(255.0f, fminf(cv[i], cap));                                  // 209
                     dc[i] = __fmul_rn(cv[i], (float)L);                                            // 289-290
                 }
                 if (a.mask && frame == 0)
