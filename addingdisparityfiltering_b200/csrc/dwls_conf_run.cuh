@@ -14,7 +14,7 @@
 #include <stdint.h>
 #include <cuda.h>
 #include "dwls_conf.cuh"
-#include "dwls_solver.cuh"
+#include "dwls_passes.cuh"
 
 namespace dwls {
 
@@ -262,7 +262,7 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
         }
         if (!LEFT) {
             float* O = a.conf_r + (size_t)frame * a.cr_frame + (size_t)y * a.cr_pitch + cx0;
-            if (nvalid == 8) { *(float4*)O = make_float4(cv[0], cv[1], cv[2], cv[3]); *((float4*)O + 1) = make_float4(cv[4], cv[5], cv[6], cv[7]); }
+            if (nvalid == 8) st_global_v8(O, cv[0], cv[1], cv[2], cv[3], cv[4], cv[5], cv[6], cv[7]);
             else
 #pragma unroll
                 for (int i = 0; i < 8; ++i) if (i < nvalid) O[i] = cv[i];
@@ -301,16 +301,16 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
                 float* PC = a.plane_c + (size_t)frame * a.p_frame + (size_t)y * a.pitch + cx0;
                 float* PD = a.plane_dc + (size_t)frame * a.p_frame + (size_t)y * a.pitch + cx0;
                 if (nvalid == 8) {
-                    *(float4*)PC = make_float4(cv[0], cv[1], cv[2], cv[3]); *((float4*)PC + 1) = make_float4(cv[4], cv[5], cv[6], cv[7]);
-                    *(float4*)PD = make_float4(dc[0], dc[1], dc[2], dc[3]); *((float4*)PD + 1) = make_float4(dc[4], dc[5], dc[6], dc[7]);
+                    st_global_v8(PC, cv[0], cv[1], cv[2], cv[3], cv[4], cv[5], cv[6], cv[7]);
+                    st_global_v8(PD, dc[0], dc[1], dc[2], dc[3], dc[4], dc[5], dc[6], dc[7]);
                 } else
 #pragma unroll
                     for (int i = 0; i < 8; ++i) if (i < nvalid) { PC[i] = cv[i]; PD[i] = dc[i]; }
             }
             if (a.conf) {
                 float* E = a.conf + (size_t)frame * a.conf_frame + (size_t)gy * a.conf_step + gx0;
-                if (nvalid == 8 && (((uintptr_t)E) & 15) == 0) {
-                    *(float4*)E = make_float4(cv[0], cv[1], cv[2], cv[3]); *((float4*)E + 1) = make_float4(cv[4], cv[5], cv[6], cv[7]);
+                if (nvalid == 8 && (((uintptr_t)E) & 31) == 0) {
+                    st_global_v8(E, cv[0], cv[1], cv[2], cv[3], cv[4], cv[5], cv[6], cv[7]);
                 } else
 #pragma unroll
                     for (int i = 0; i < 8; ++i) if (i < nvalid) E[i] = cv[i];

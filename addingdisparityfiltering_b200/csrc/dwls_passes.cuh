@@ -53,20 +53,21 @@ __device__ __forceinline__ uint8_t cvt_u8(float v)
     return (uint8_t)max(0, min(255, i));
 }
 // disparity_filters.cpp:295: d*c~ .mul( 1 / (c~ + EPS) ), EPS = 1e-43f (denormal, line 47)
+__device__ __forceinline__ float wls_den(float c) { return __fadd_rn(fmaxf(c, 0.0f), __int_as_float(71)); }   // 71 * 2^-149 == 1e-43f
+// den and 1/den both normal numbers (2^-126 <= den < 2^125): one unsigned compare on the bit pattern (den >= 0)
+__device__ __forceinline__ bool wls_den_normal(float den) { return (uint32_t)(__float_as_int(den) - 0x00800000) < (uint32_t)(0x7e000000 - 0x00800000); }
+// MUFU.RCP and one Newton step: the correctly rounded reciprocal (up to ties 2^-22 apart), which is what the
+// reference's IEEE division returns; only valid when wls_den_normal(den)
+__device__ __forceinline__ float wls_rcp_fast(float den)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(den));
+    return fmaf(r, fmaf(-den, r, 1.0f), r);
+}
 __device__ __forceinline__ float wls_normalise(float dc, float c)
 {
-    const float den = __fadd_rn(fmaxf(c, 0.0f), __int_as_float(71));   // 71 * 2^-149 == 1e-43f
-    float rec;
-    if (den >= 1.1754944e-38f && den <= 8.0e37f) {
-        // den and 1/den are normal numbers: MUFU.RCP and one Newton step give the correctly rounded reciprocal
-        // (up to ties 2^-22 apart), which is what the reference's IEEE division returns
-        float r;
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(den));
-        rec = fmaf(r, fmaf(-den, r, 1.0f), r);
-    } else {
-        rec = __fdiv_rn(1.0f, den);
-    }
-    return __fmul_rn(dc, rec);
+    const float den = wls_den(c);
+    return __fmul_rn(dc, wls_den_normal(den) ? wls_rcp_fast(den) : __fdiv_rn(1.0f, den));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -373,12 +374,14 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
                 }
             } else {
                 int16_t* O = a.out16 + (size_t)frame * a.out16_frame + (size_t)r0 * a.out16_step + col;
+                if (nrow == M) {
 #pragma unroll
-                for (int m = 0; m < M; ++m)
-                    if (m < nrow) {
-                        const float val = (FIN == FIN_WLS) ? wls_normalise(f[0][m], f[S - 1][m]) : f[0][m];
-                        O[(size_t)m * a.out16_step] = cvt_s16(val);
-                    }
+                    for (int m = 0; m < M; ++m) O[(size_t)m * a.out16_step] = cvt_s16((FIN == FIN_WLS) ? wls_normalise(f[0][m], f[S - 1][m]) : f[0][m]);
+                } else {
+#pragma unroll
+                    for (int m = 0; m < M; ++m)
+                        if (m < nrow) O[(size_t)m * a.out16_step] = cvt_s16((FIN == FIN_WLS) ? wls_normalise(f[0][m], f[S - 1][m]) : f[0][m]);
+                }
             }
         }
     }
