@@ -839,6 +839,27 @@ extern "C" dwls_status dwls_fgs_weights_host(dwls_ctx* ctx, const dwls_image* gu
     return DWLS_OK;
 }
 
+// nf frames of `rows` rows of `row_bytes` between host and device: one transfer when both sides are dense, else one per
+// frame (dense rows) or a 2-D copy per frame.  dst_step < 0: the destination rows are dense (device staging).
+static dwls_status copy_frames(dwls_ctx* ctx, void* dst, int64_t dst_frame, const void* src, int64_t src_frame, int64_t src_step,
+                               size_t row_bytes, int rows, int nf, cudaMemcpyKind kind, cudaStream_t st, int64_t dst_step = -1)
+{
+    if (dst_step < 0) dst_step = (int64_t)row_bytes;
+    const bool dense_rows = src_step == (int64_t)row_bytes && dst_step == (int64_t)row_bytes;
+    const int64_t frame_bytes = (int64_t)row_bytes * rows;
+    if (dense_rows && (nf == 1 || (src_frame == frame_bytes && dst_frame == frame_bytes))) {
+        CK(cudaMemcpyAsync(dst, src, (size_t)frame_bytes * nf, kind, st));
+        return DWLS_OK;
+    }
+    for (int f = 0; f < nf; ++f) {
+        uint8_t* d = (uint8_t*)dst + (size_t)f * dst_frame;
+        const uint8_t* s = (const uint8_t*)src + (size_t)f * src_frame;
+        if (dense_rows) CK(cudaMemcpyAsync(d, s, (size_t)frame_bytes, kind, st));
+        else CK(cudaMemcpy2DAsync(d, (size_t)dst_step, s, (size_t)src_step, row_bytes, rows, kind, st));
+    }
+    return DWLS_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // batch of frames in HOST memory (pinned for full speed): two lanes, each with its own stream,
 // staging area and workspace, so the H2D copy of one group overlaps the kernels and the D2H copy
@@ -860,7 +881,7 @@ extern "C" dwls_status dwls_filter_batch_host(dwls_ctx* ctx, const dwls_batch* h
     const int dw = g.dw, dh = g.dh, W = g.W, H = g.H, vcn = g.vcn;
     const WsLayout L = ws_layout(g, useconf);
     int G = pick_group(ctx, L.per_frame * sizeof(float), hb->n_frames);
-    if (ctx->group_frames == 0 && G > 8) G = 8;           // smaller groups pipeline better against PCIe
+    if (ctx->group_frames == 0 && G > 8) G = 8;           // smaller groups pipeline better against PCIe (the path is H2D-bound)
     const size_t f_dl = align256((size_t)dw * dh * 2), f_view = align256((size_t)W * H * vcn), f_out = align256((size_t)W * H * 2),
                  f_conf = want_conf ? align256((size_t)W * H * 4) : 0;
     const size_t lane_stage = (size_t)G * (2 * f_dl + f_view + f_out + f_conf);
@@ -871,17 +892,20 @@ extern "C" dwls_status dwls_filter_batch_host(dwls_ctx* ctx, const dwls_batch* h
     CK(cudaStreamSynchronize(ctx->stream));
     cudaStream_t lanes[2] = { ctx->stream, ctx->stream2 };
     int lane = 0;
-    for (int f0 = 0; f0 < hb->n_frames; f0 += G, lane ^= 1) {
-        const int nf = (hb->n_frames - f0 < G) ? hb->n_frames - f0 : G;
+    // the H2D engine is the bottleneck and stays busy back to back; what is exposed is the tail (kernels + D2H of the
+    // last group), so the last G frames go out in halving groups (.., G/2, .., 1, 1)
+    for (int f0 = 0, nf = 0; f0 < hb->n_frames; f0 += nf, lane ^= 1) {
+        const int left = hb->n_frames - f0;
+        nf = left > G ? G : (left + 1) / 2;
         cudaStream_t st = lanes[lane];
         uint8_t* d = (uint8_t*)ctx->stage + lane * lane_stage;
         uint8_t* d_dl = d; uint8_t* d_dr = d_dl + (size_t)G * f_dl; uint8_t* d_view = d_dr + (size_t)G * f_dl;
         uint8_t* d_out = d_view + (size_t)G * f_view; uint8_t* d_conf = d_out + (size_t)G * f_out;
-        for (int f = 0; f < nf; ++f) {
-            const size_t hf = (size_t)(f0 + f);
-            CK(cudaMemcpy2DAsync(d_dl + f * f_dl, (size_t)dw * 2, (const uint8_t*)hb->disp_left + hf * hb->dl_frame, hb->dl_step, (size_t)dw * 2, dh, cudaMemcpyHostToDevice, st));
-            if (useconf) CK(cudaMemcpy2DAsync(d_dr + f * f_dl, (size_t)dw * 2, (const uint8_t*)hb->disp_right + hf * hb->dr_frame, hb->dr_step, (size_t)dw * 2, dh, cudaMemcpyHostToDevice, st));
-            CK(cudaMemcpy2DAsync(d_view + f * f_view, (size_t)W * vcn, hb->view + hf * hb->view_frame, hb->view_step, (size_t)W * vcn, H, cudaMemcpyHostToDevice, st));
+        {
+            dwls_status cs;
+            if ((cs = copy_frames(ctx, d_dl, f_dl, (const uint8_t*)hb->disp_left + (size_t)f0 * hb->dl_frame, hb->dl_frame, hb->dl_step, (size_t)dw * 2, dh, nf, cudaMemcpyHostToDevice, st))) return cs;
+            if (useconf && (cs = copy_frames(ctx, d_dr, f_dl, (const uint8_t*)hb->disp_right + (size_t)f0 * hb->dr_frame, hb->dr_frame, hb->dr_step, (size_t)dw * 2, dh, nf, cudaMemcpyHostToDevice, st))) return cs;
+            if ((cs = copy_frames(ctx, d_view, f_view, hb->view + (size_t)f0 * hb->view_frame, hb->view_frame, hb->view_step, (size_t)W * vcn, H, nf, cudaMemcpyHostToDevice, st))) return cs;
         }
         dwls_batch b;
         memset(&b, 0, sizeof b);
@@ -893,10 +917,10 @@ extern "C" dwls_status dwls_filter_batch_host(dwls_ctx* ctx, const dwls_batch* h
         b.out = (int16_t*)d_out; b.out_step = (int64_t)W * 2; b.out_frame = (int64_t)f_out;
         b.conf = want_conf ? (float*)d_conf : nullptr; b.conf_step = (int64_t)W * 4; b.conf_frame = (int64_t)f_conf;
         if ((s = filter_frames(ctx, &b, 0, nf, g, p, nullptr, 0, false, st, (float*)((uint8_t*)ctx->ws + lane * lane_ws)))) return s;
-        for (int f = 0; f < nf; ++f) {
-            const size_t hf = (size_t)(f0 + f);
-            CK(cudaMemcpy2DAsync((uint8_t*)hb->out + hf * hb->out_frame, hb->out_step, d_out + f * f_out, (size_t)W * 2, (size_t)W * 2, H, cudaMemcpyDeviceToHost, st));
-            if (want_conf) CK(cudaMemcpy2DAsync((uint8_t*)hb->conf + hf * hb->conf_frame, hb->conf_step, d_conf + f * f_conf, (size_t)W * 4, (size_t)W * 4, H, cudaMemcpyDeviceToHost, st));
+        {
+            dwls_status cs;
+            if ((cs = copy_frames(ctx, (uint8_t*)hb->out + (size_t)f0 * hb->out_frame, hb->out_frame, d_out, f_out, (int64_t)W * 2, (size_t)W * 2, H, nf, cudaMemcpyDeviceToHost, st, hb->out_step))) return cs;
+            if (want_conf && (cs = copy_frames(ctx, (uint8_t*)hb->conf + (size_t)f0 * hb->conf_frame, hb->conf_frame, d_conf, f_conf, (int64_t)W * 4, (size_t)W * 4, H, nf, cudaMemcpyDeviceToHost, st, hb->conf_step))) return cs;
         }
     }
     CK(cudaStreamSynchronize(ctx->stream));
