@@ -179,3 +179,45 @@ def test_error_behaviour(ctx):
     assert e.value.status == 2                                           # StsBadSize (185-189)
     with pytest.raises(A.DwlsError):
         A.fastGlobalSmootherFilter(view, dl, -1.0, 1.0, ctx=ctx)         # lambda >= 0 (143)
+
+
+@pytest.mark.parametrize("radius", [0, 1, 2, 3, 4, 5, 6, 7, 8, 9])
+@pytest.mark.parametrize("size", [(320, 96), (127, 61)])          # 16-byte-aligned rows (TMA tile path) / unaligned rows (plain-load path)
+def test_confidence_stage_radii_and_alignments(ctx, radius, size):
+    # box-variance + LRC stage alone (disparity_filters.cpp:161-210, 306-373): every radius of the register kernel (0..7),
+    # the shared-memory kernel (8, 9), ROI origins at every residue mod 8 (in-place realignment after the aligned TMA
+    # fetch), ROIs touching the image border and ROIs narrower/shorter than the halo (multi-bounce reflect-101)
+    w, h = size
+    view, dl, dr, _ = synth.make_artificial_example(w, h, 1, seed=31 * radius + w)
+    rng = np.random.default_rng(radius + w)
+    dl = (dl.astype(np.int32) + rng.integers(-40, 40, dl.shape)).astype(np.int16)
+    dr = (dr.astype(np.int32) + rng.integers(-40, 40, dr.shape)).astype(np.int16)
+    rois = [(0, 0, w, h), (3 + radius, 1, w - 11 - radius, h - 2), (w // 3 + 5, h // 4, w // 2 + 2, h // 2 + 1), (w - 13, h - 7, 13, 7),
+            (17, 5, 3, 2), (40, 2, w - 47, 1)]
+    f = A.createDisparityWLSFilterGeneric(True, ctx=ctx)
+    f.setDepthDiscontinuityRadius(radius)
+    for roi in rois:
+        got = f.filter(dl, view, None, dr, roi)
+        ref = O.wls_filter(dl, view, dr, roi=roi, lam=8000.0, sigma=1.0, lrc_thresh=24, disc_radius=radius, want_mask=True)
+        assert ref["rc"] == 0
+        assert (f.lrc_mask(dl, dr, ROI=roi) == ref["mask"]).all(), (radius, roi)
+        assert np.abs(f.getConfidenceMap() - ref["conf"]).max() <= 1e-4, (radius, roi)
+        assert_s16_parity(got, ref["out"], roi)
+
+
+def test_confidence_extreme_values(ctx):
+    # |d| up to 32767 / -32768: window sums of squares need more than 32 bits; the LRC sum L + R must not wrap
+    w, h = 320, 64
+    rng = np.random.default_rng(5)
+    view = rng.integers(0, 256, (h, w)).astype(np.uint8)
+    dl = rng.integers(-32768, 32768, (h, w)).astype(np.int16)
+    dr = rng.integers(-32768, 32768, (h, w)).astype(np.int16)
+    dl[:8] = -32768; dr[:8] = -32768; dl[8:16] = 32767; dr[8:16] = -32767
+    f = A.createDisparityWLSFilterGeneric(True, ctx=ctx)
+    for radius in (2, 7):
+        f.setDepthDiscontinuityRadius(radius)
+        roi = (8, 0, w - 16, h)
+        f.filter(dl, view, None, dr, roi)
+        ref = O.wls_filter(dl, view, dr, roi=roi, lam=8000.0, sigma=1.0, lrc_thresh=24, disc_radius=radius, want_mask=True)
+        assert (f.lrc_mask(dl, dr, ROI=roi) == ref["mask"]).all()
+        assert np.abs(f.getConfidenceMap() - ref["conf"]).max() <= 1e-4
