@@ -1,0 +1,99 @@
+"""GPU parity of the batch entry points (dwls_filter_batch_dev / dwls_filter_batch_host) against the CPU oracle,
+frame by frame: independent frames of a batch must come out exactly as single filter() calls would
+(disparity_filters.cpp keeps no state between calls except the getters, :138-139)."""
+import numpy as np
+import pytest
+
+from addingdisparityfiltering_b200 import synth
+from addingdisparityfiltering_b200.batch import BatchFilter
+from oracle import oracle as O
+from tests.parity import assert_s16_parity
+
+pytestmark = pytest.mark.gpu
+
+
+def _frames(n, w, h, cn, seed):
+    fr = [synth.make_textured_scene(w, h, cn, seed=seed + i, max_disp=max(32, w // 8)) for i in range(n)]
+    return (np.stack([f[0] for f in fr]), np.stack([f[1] for f in fr]), np.stack([f[2] for f in fr]))
+
+
+@pytest.mark.parametrize("size,radius", [((320, 240), 2), ((328, 122), 5), ((127, 61), 3)])
+@pytest.mark.parametrize("strided", [False, True])
+def test_batch_device_matches_oracle(ctx, size, radius, strided):
+    import torch
+    w, h = size
+    n = 5
+    view, dl, dr = _frames(n, w, h, 3, seed=100 + w)
+    md = max(32, w // 8)
+    roi = (md + 3, 2, w - md - 7, h - 5)
+    dev = torch.device("cuda", 0)
+
+    def put(a, pad_rows, pad_cols):
+        # strided: frames and rows live inside a larger allocation (cv::Mat ROI views / padded batches)
+        t = torch.from_numpy(a).to(dev)
+        if not strided:
+            return t
+        shape = list(t.shape)
+        big = torch.zeros([shape[0], shape[1] + pad_rows, shape[2] + pad_cols] + shape[3:], dtype=t.dtype, device=dev)
+        v = big[:, 1:1 + shape[1], 8:8 + shape[2]]
+        v.copy_(t)
+        return v
+    tv, tl, tr = put(view, 3, 24), put(dl, 2, 16), put(dr, 1, 8)
+    out = put(np.zeros((n, h, w), np.int16), 2, 16)
+    conf = put(np.zeros((n, h, w), np.float32), 2, 16)
+    bf = BatchFilter(True, 8000.0, 1.5, 24, radius, ctx=ctx)
+    ctx.set_group_frames(2)                      # 5 frames -> groups 2 + 2 + 1
+    try:
+        bf.filter_device(tl, tv, out, tr, conf, roi)
+        torch.cuda.synchronize()
+    finally:
+        ctx.set_group_frames(0)
+    assert tuple(bf.roi) == roi
+    for i in range(n):
+        ref = O.wls_filter(dl[i], view[i], dr[i], roi=roi, lam=8000.0, sigma=1.5, lrc_thresh=24, disc_radius=radius)
+        assert np.abs(conf[i].cpu().numpy() - ref["conf"]).max() <= 1e-4
+        assert_s16_parity(out[i].cpu().numpy(), ref["out"], roi)
+
+
+@pytest.mark.parametrize("use_conf", [True, False])
+def test_batch_host_matches_device_and_oracle(ctx, use_conf):
+    import torch
+    w, h, n = 320, 240, 11                       # 11 frames: groups 8, 2, 1 on the host path
+    view, dl, dr = _frames(n, w, h, 3, seed=7)
+    roi = (40, 0, w - 40, h)
+    bf = BatchFilter(use_conf, 8000.0, 1.5, 24, 2, ctx=ctx)
+    out_h = np.zeros((n, h, w), np.int16)
+    conf_h = np.zeros((n, h, w), np.float32) if use_conf else None
+    bf.filter_host(dl, view, out_h, dr if use_conf else None, conf_h, roi)
+    dev = torch.device("cuda", 0)
+    out_d = torch.zeros((n, h, w), dtype=torch.int16, device=dev)
+    bf.filter_device(torch.from_numpy(dl).to(dev), torch.from_numpy(view).to(dev), out_d,
+                     torch.from_numpy(dr).to(dev) if use_conf else None, None, roi)
+    torch.cuda.synchronize()
+    assert (out_d.cpu().numpy() == out_h).all()  # same kernels, same result bit for bit
+    for i in (0, 5, 10):
+        ref = O.wls_filter(dl[i], view[i], dr[i], roi=roi, use_confidence=use_conf, lam=8000.0, sigma=1.5, lrc_thresh=24, disc_radius=2)
+        assert_s16_parity(out_h[i], ref["out"], roi)
+        if use_conf:
+            assert np.abs(conf_h[i] - ref["conf"]).max() <= 1e-4
+
+
+def test_batch_half_res_device(ctx):
+    import cv2
+    import torch
+    w, h, n = 320, 240, 3
+    view, dl, dr = _frames(n, w, h, 3, seed=21)
+    dl2 = np.stack([(cv2.resize(d, None, fx=0.5, fy=0.5) // 2).astype(np.int16) for d in dl])
+    dr2 = np.stack([(cv2.resize(d, None, fx=0.5, fy=0.5) // 2).astype(np.int16) for d in dr])
+    roi = (20, 1, w // 2 - 23, h // 2 - 2)
+    dev = torch.device("cuda", 0)
+    out = torch.zeros((n, h, w), dtype=torch.int16, device=dev)
+    conf = torch.zeros((n, h, w), dtype=torch.float32, device=dev)
+    bf = BatchFilter(True, 8000.0, 1.5, 24, 3, ctx=ctx)
+    bf.filter_device(torch.from_numpy(dl2).to(dev), torch.from_numpy(view).to(dev), out, torch.from_numpy(dr2).to(dev), conf, roi)
+    torch.cuda.synchronize()
+    froi = (roi[0] * 2, roi[1] * 2, roi[2] * 2, roi[3] * 2)
+    for i in range(n):
+        ref = O.wls_filter(dl2[i], view[i], dr2[i], roi=roi, lam=8000.0, sigma=1.5, lrc_thresh=24, disc_radius=3)
+        assert np.abs(conf[i].cpu().numpy() - ref["conf"]).max() <= 1e-4
+        assert_s16_parity(out[i].cpu().numpy(), ref["out"], froi)
