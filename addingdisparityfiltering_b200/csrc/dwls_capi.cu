@@ -184,12 +184,13 @@ static dwls_status ensure_lut(dwls_ctx* ctx, float sigma, cudaStream_t st)
     return DWLS_OK;
 }
 
-struct SolvePlan { int hK; int vM, vCols, vK; };
+struct SolvePlan { int hK, hM; int vM, vCols, vK; };
 
 static bool plan_solver(int w, int h, SolvePlan* p)
 {
-    p->hK = round_up((w + HM - 1) / HM, 32);
-    if (p->hK > 1024) return false;
+    p->hM = w <= 2048 ? 8 : 16;
+    p->hK = round_up((w + p->hM - 1) / p->hM, 32);
+    if (p->hK > 512) return false;
     if (h <= 9 * 128) { p->vM = 9; p->vCols = 8; }
     else if (h <= 17 * 128) { p->vM = 17; p->vCols = 4; }
     else return false;
@@ -197,11 +198,11 @@ static bool plan_solver(int w, int h, SolvePlan* p)
     return true;
 }
 
-template <int S, int MAXT>
+template <int S, int MAXT, int HM>
 static dwls_status launch_h_inst(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
-    const size_t smem = hsolve_smem_bytes<S>(pl.hK, a.pitch);
-    auto k = hsolve_kernel<S, MAXT>;
+    const size_t smem = hsolve_smem_bytes<S, HM>(pl.hK, a.pitch);
+    auto k = hsolve_kernel<S, MAXT, HM>;
     static int ctas_per_sm = 0, cached_K = 0; static size_t cached_smem = 0;
     if (smem > 227 * 1024) return fail(ctx, DWLS_UNSUPPORTED, "row too wide for the shared-memory stages of the row pass");
     if (!ctas_per_sm || cached_K != pl.hK || cached_smem != smem) {
@@ -222,9 +223,9 @@ static dwls_status launch_h_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
 template <int S>
 static dwls_status launch_h(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
-    if (pl.hK <= 256) return launch_h_inst<S, 256>(ctx, a, pl, frames, st);
-    if (pl.hK <= 512) return launch_h_inst<S, 512>(ctx, a, pl, frames, st);
-    return launch_h_inst<S, 1024>(ctx, a, pl, frames, st);
+    if (pl.hM == 8) return launch_h_inst<S, 256, 8>(ctx, a, pl, frames, st);          // w <= 2048
+    if (pl.hK <= 256) return launch_h_inst<S, 256, 16>(ctx, a, pl, frames, st);       // w <= 4096
+    return launch_h_inst<S, 512, 16>(ctx, a, pl, frames, st);                         // w <= 8192: level 2 takes the generic loop
 }
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda)

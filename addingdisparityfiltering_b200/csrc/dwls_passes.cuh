@@ -10,10 +10,8 @@
 
 namespace dwls {
 
-#ifndef DWLS_HM
-#define DWLS_HM 8
-#endif
-constexpr int HM = DWLS_HM;  // elements per thread in the row solve (HM/4 float4 per plane)
+// elements per thread in the row solve: 8 (one 32-byte sector per plane) up to 2048 columns, 16 for wider rows so
+// that the reduced system still has at most 256 rows (level 2 in registers, 8 rows per lane)
 constexpr int MAXS = 4;      // planes solved together (fgs_filter.cpp:184: channels <= 4)
 
 struct SolveArgs {
@@ -92,14 +90,14 @@ constexpr int HL2BUF = DWLS_HL2BUF; // level-2 scratch copies (1 needs a third b
 constexpr int HST = DWLS_HST;      // shared-memory stages per CTA
 constexpr int HMINB = DWLS_HMINB;  // CTAs per SM the row pass is compiled for (register cap)
 
-template <int S>
+template <int S, int HM>
 __host__ __device__ inline size_t hsolve_smem_bytes(int K, int pitch)
 {
     return sizeof(float) * ((size_t)HST * (1 + S) * pitch + HL2BUF * (size_t)(4 + 2 * S) * l2pad_size(K) + 32 * (2 + S) * HM) + sizeof(uint64_t) * HST;
 }
 
-template <int S, int MAXT>
-__global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? HMINB : 1)) hsolve_kernel(const SolveArgs a, const int rows_total)
+template <int S, int MAXT, int HM>
+__global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : 2) : 1)) hsolve_kernel(const SolveArgs a, const int rows_total)
 {
     extern __shared__ __align__(128) float sm[];
     const int K = blockDim.x, M2 = K >> 5, KP = l2pad_size(K);
@@ -215,12 +213,9 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? HMINB : 1)) hsolve_kernel
 #pragma unroll
             for (int s = 0; s < S; ++s) {
                 float* P = a.out[s] + (size_t)frame * a.p_frame + (size_t)row * a.pitch + j0;
-                if (HM == 8) {
-                    st_global_v8(P, f[s][0], f[s][1], f[s][2], f[s][3], f[s][4], f[s][5], f[s][6], f[s][7]);     // one full 32-byte sector per thread
-                } else {
 #pragma unroll
-                    for (int q = 0; q < HM / 4; ++q) *((float4*)P + q) = make_float4(f[s][4 * q], f[s][4 * q + 1], f[s][4 * q + 2], f[s][4 * q + 3]);
-                }
+                for (int q = 0; q < HM / 8; ++q)                  // full 32-byte sectors, one 256-bit store each
+                    if (q == 0 || j0 + 8 * q < a.pitch) st_global_v8(P + 8 * q, f[s][8 * q], f[s][8 * q + 1], f[s][8 * q + 2], f[s][8 * q + 3], f[s][8 * q + 4], f[s][8 * q + 5], f[s][8 * q + 6], f[s][8 * q + 7]);
             }
         }
     }
