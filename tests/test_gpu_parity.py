@@ -221,3 +221,18 @@ def test_confidence_extreme_values(ctx):
         ref = O.wls_filter(dl, view, dr, roi=roi, lam=8000.0, sigma=1.0, lrc_thresh=24, disc_radius=radius, want_mask=True)
         assert (f.lrc_mask(dl, dr, ROI=roi) == ref["mask"]).all()
         assert np.abs(f.getConfidenceMap() - ref["conf"]).max() <= 1e-4
+
+
+@pytest.mark.parametrize("size", [(2500, 40), (4096, 33), (3840, 48), (5000, 24), (8192, 16), (64, 2000), (40, 1153), (200, 2176)])
+@pytest.mark.parametrize("planes", [1, 2])
+def test_fgs_wide_and_tall_images(ctx, size, planes):
+    # rows wider than 2048 take the 16-elements-per-thread row pass (> 4096: 512 threads, looped level 2);
+    # more than 1152 rows take the 17-rows-per-thread column pass
+    w, h = size
+    rng = np.random.default_rng(w + h)
+    g = _guide(rng, h, w, 3)
+    shape = (h, w) if planes == 1 else (h, w, planes)
+    src = (rng.random(shape) * 255).astype(np.float32)
+    got = A.fastGlobalSmootherFilter(g, src, 8000.0, 1.5, ctx=ctx)
+    ref = O.fgs_filter(g, src, 8000.0, 1.5)
+    assert np.abs(got - ref).max() <= 255 * 1e-3
