@@ -290,9 +290,9 @@ static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
 template <int S, int FIN>
 static dwls_status launch_v(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
-    static const int vc4 = getenv("DWLS_VC4") ? atoi(getenv("DWLS_VC4")) : 0;
-    if (pl.vM == 9 && vc4) return launch_v_inst<9, S, 4, FIN, 512>(ctx, a, pl, frames, st);
     if (pl.vM == 9) return launch_v_inst<9, S, 8, FIN, 1024>(ctx, a, pl, frames, st);
+    // 1153..2176 rows, 17 rows per thread: a single plane still fits 8-column strips (32-byte rows) in 64 registers
+    if (pl.vCols == 4 && S == 1) return launch_v_inst<17, 1, 8, FIN == FIN_WLS ? FIN_FLOAT : FIN, 1024>(ctx, a, pl, frames, st);
     if (pl.vCols == 4) return launch_v_inst<17, S, 4, FIN, 512>(ctx, a, pl, frames, st);
     return fail(ctx, DWLS_UNSUPPORTED, "column pass supports at most 2176 rows");
 }
