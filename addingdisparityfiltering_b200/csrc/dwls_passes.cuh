@@ -153,12 +153,17 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : 2) : 1
                     f[s][4 * q] = ff.x; f[s][4 * q + 1] = ff.y; f[s][4 * q + 2] = ff.z; f[s][4 * q + 3] = ff.w;
                 }
             }
+            if (j0 + HM < a.w) {                                       // chunk strictly inside the row: no masks
 #pragma unroll
-            for (int k = 0; k < HM; ++k) {
-                c[k] = (j0 + k < a.w - 1) ? a.lam * c[k] : 0.f;      // last weight of a line is 0 (fgs_filter.cpp:614)
-                if (j0 + k >= a.w) {
+                for (int k = 0; k < HM; ++k) c[k] = a.lam * c[k];
+            } else {
 #pragma unroll
-                    for (int s = 0; s < S; ++s) f[s][k] = 0.f;
+                for (int k = 0; k < HM; ++k) {
+                    c[k] = (j0 + k < a.w - 1) ? a.lam * c[k] : 0.f;  // last weight of a line is 0 (fgs_filter.cpp:614)
+                    if (j0 + k >= a.w) {
+#pragma unroll
+                        for (int s = 0; s < S; ++s) f[s][k] = 0.f;
+                    }
                 }
             }
         } else {
