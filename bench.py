@@ -267,8 +267,16 @@ def main():
     dom_name, (dom_n, dom_ms) = dom
     frames_per_launch = B * args.steps * {"hsolve_kernel": 3, "vsolve_kernel": 2}.get(dom_name, 1) / dom_n
     achieved = per_alg.get(dom_name, 0) * frames_per_launch / (dom_ms / dom_n * 1e-3) / 1e9
+    # DRAM bytes of the dominant kernel per launch from the committed ncu --set full capture (profiles/ncu_traffic_r01.json)
+    traffic = None
+    try:
+        tk = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic_r01.json")))["kernels"].get(dom_name)
+        if tk:
+            traffic = tk["dram_bytes_per_frame"] * frames_per_launch
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "alg_bytes_per_launch": per_alg.get(dom_name, 0) * frames_per_launch,
+                "traffic": traffic, "peak_source": peak_src, "alg_bytes_per_launch": per_alg.get(dom_name, 0) * frames_per_launch,
                 "avg_launch_ms": dom_ms / dom_n,
                 "pipeline": {"alg_bytes_per_frame": total_alg, "achieved": total_alg * B * args.steps / (ms * 1e-3) / 1e9,
                              "frac": total_alg * B * args.steps / (ms * 1e-3) / 1e9 / peak},
