@@ -35,7 +35,7 @@ __device__ __forceinline__ float rcp_nr(float x)
 }
 
 // pivots of both levels use the bare MUFU.RCP: relative error <= 2^-23, one float rounding's worth next to the dozens
-// of roundings a solve already accumulates.  Measured at 1080p against the oracle: 99.9924 % of the CV_16S outputs
+// of roundings a solve already accumulates.  Measured at 1080p against the CPU reference restatement: 99.9924 % of the CV_16S outputs
 // identical, 100 % within 1 LSB (with a Newton step per pivot: 99.9930 %), for two dependent FMAs less per step.
 __device__ __forceinline__ float rcp_l2(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 
