@@ -544,7 +544,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
         u.fx = g.fx; u.fy = g.fy; u.fw = g.fw; u.fh = g.fh;
         u.conf = conf ? cexp : nullptr; u.conf_step = b->conf_step / 4; u.conf_frame = b->conf_frame / 4;
         u.plane_dc = p0; u.plane_c = conf ? p1 : nullptr; u.p_frame = L.plane; u.pitch = g.pitch;
-        TIMED(K_UPSCALE, st, upscale_prep_kernel<<<dim3((g.W + 255) / 256, g.H, nf), 256, 0, st>>>(u));
+        TIMED(K_UPSCALE, st, upscale_prep_kernel<<<dim3((upscale_groups(g.W, g.fx) + 127) / 128, g.H, nf), 128, 0, st>>>(u));
         CK(cudaGetLastError());
     } else if (!conf) {
         TIMED(K_PREP, st, prep_noconf_kernel<<<dim3((g.fw + 255) / 256, g.fh, nf), 256, 0, st>>>(dl + (size_t)g.fy * (b->dl_step / 2) + g.fx, b->dl_step / 2,

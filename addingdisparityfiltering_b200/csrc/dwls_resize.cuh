@@ -42,32 +42,60 @@ struct UpArgs {
     float* plane_dc; float* plane_c; int64_t p_frame; int pitch;   // plane_c NULL in the no-confidence path
 };
 
-// grid = (ceil(W/256), H, frames).  Only ROI pixels need the disparity; the confidence export
-// needs every pixel.
-__global__ void __launch_bounds__(256) upscale_prep_kernel(const UpArgs a)
+// grid = (ceil(groups/128), H, frames), block 128: a thread takes 4 consecutive view columns, the groups being aligned
+// to the ROI origin (X = fx % 4 - 4 + 4 * group) so that the plane stores are aligned float4.  Only ROI pixels need the
+// disparity; the confidence export needs every pixel.
+__host__ __device__ inline int upscale_groups(int W, int fx) { return (W - ((fx & 3) - 4) + 3) / 4; }
+
+__global__ void __launch_bounds__(128) upscale_prep_kernel(const UpArgs a)
 {
-    const int X = blockIdx.x * blockDim.x + threadIdx.x, Y = blockIdx.y, frame = blockIdx.z;
-    if (X >= a.W) return;
-    const bool in_roi = X >= a.fx && X < a.fx + a.fw && Y >= a.fy && Y < a.fy + a.fh;
-    if (!in_roi && !(a.conf && a.conf_lo)) return;
-    const Lin cx = lin_coeff(X, a.scale_x, a.dw, true), cy = lin_coeff(Y, a.scale_y, a.dh, false);
+    const int grp = blockIdx.x * blockDim.x + threadIdx.x, Y = blockIdx.y, frame = blockIdx.z;
+    const int X0 = (a.fx & 3) - 4 + 4 * grp;
+    if (X0 >= a.W) return;
+    const bool row_in = Y >= a.fy && Y < a.fy + a.fh;
+    const bool any_roi = row_in && X0 + 3 >= a.fx && X0 < a.fx + a.fw;
+    const bool want_conf = a.conf && a.conf_lo;
+    if (!any_roi && !want_conf) return;
+    const Lin cy = lin_coeff(Y, a.scale_y, a.dh, false);
     const int y0 = min(max(cy.s, 0), a.dh - 1), y1 = min(max(cy.s + 1, 0), a.dh - 1);
     const float b1 = cy.f, b0 = __fsub_rn(1.f, b1);
-    float cval = 0.f;
-    if (a.conf_lo) {
-        const float* c = a.conf_lo + (size_t)frame * a.cl_frame;
-        const float h0 = lin_h(c + (size_t)y0 * a.cl_step, cx, a.dw), h1 = lin_h(c + (size_t)y1 * a.cl_step, cx, a.dw);
-        cval = __fadd_rn(__fmul_rn(h0, b0), __fmul_rn(h1, b1));
-        if (a.conf) a.conf[(size_t)frame * a.conf_frame + (size_t)Y * a.conf_step + X] = cval;
+    const float* c0 = a.conf_lo ? a.conf_lo + (size_t)frame * a.cl_frame + (size_t)y0 * a.cl_step : nullptr;
+    const float* c1 = a.conf_lo ? a.conf_lo + (size_t)frame * a.cl_frame + (size_t)y1 * a.cl_step : nullptr;
+    const int16_t* d0 = a.disp + (size_t)frame * a.d_frame + (size_t)y0 * a.d_step;
+    const int16_t* d1 = a.disp + (size_t)frame * a.d_frame + (size_t)y1 * a.d_step;
+    float cval[4] = { 0.f, 0.f, 0.f, 0.f }, dcv[4] = { 0.f, 0.f, 0.f, 0.f };
+    bool roi[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int X = X0 + q;
+        roi[q] = row_in && X >= a.fx && X < a.fx + a.fw;
+        if (X < 0 || X >= a.W) continue;
+        if (!roi[q] && !want_conf) continue;
+        const Lin cx = lin_coeff(X, a.scale_x, a.dw, true);
+        if (a.conf_lo) cval[q] = __fadd_rn(__fmul_rn(lin_h(c0, cx, a.dw), b0), __fmul_rn(lin_h(c1, cx, a.dw), b1));
+        if (roi[q]) {
+            const int16_t up = cvt_s16(__fadd_rn(__fmul_rn(lin_h(d0, cx, a.dw), b0), __fmul_rn(lin_h(d1, cx, a.dw), b1)));   // resize -> CV_16S
+            const float dv = (float)cvt_s16(__fmul_rn((float)up, a.x_ratio));                                            // disp * x_ratio -> CV_16S (244/273)
+            dcv[q] = a.plane_c ? __fmul_rn(cval[q], dv) : dv;
+        }
     }
-    if (!in_roi) return;
-    const int16_t* d = a.disp + (size_t)frame * a.d_frame;
-    const float h0 = lin_h(d + (size_t)y0 * a.d_step, cx, a.dw), h1 = lin_h(d + (size_t)y1 * a.d_step, cx, a.dw);
-    const int16_t up = cvt_s16(__fadd_rn(__fmul_rn(h0, b0), __fmul_rn(h1, b1)));          // resize -> CV_16S
-    const float dv = (float)cvt_s16(__fmul_rn((float)up, a.x_ratio));                     // disp * x_ratio -> CV_16S (244/273)
-    const size_t po = (size_t)frame * a.p_frame + (size_t)(Y - a.fy) * a.pitch + (X - a.fx);
-    if (a.plane_c) { a.plane_c[po] = cval; a.plane_dc[po] = __fmul_rn(cval, dv); }
-    else a.plane_dc[po] = dv;
+    if (want_conf) {
+        float* E = a.conf + (size_t)frame * a.conf_frame + (size_t)Y * a.conf_step + X0;
+        if (X0 >= 0 && X0 + 3 < a.W && (((uintptr_t)E) & 15) == 0) *(float4*)E = make_float4(cval[0], cval[1], cval[2], cval[3]);
+        else
+#pragma unroll
+            for (int q = 0; q < 4; ++q) if (X0 + q >= 0 && X0 + q < a.W) E[q] = cval[q];
+    }
+    if (!any_roi) return;
+    const size_t po = (size_t)frame * a.p_frame + (size_t)(Y - a.fy) * a.pitch + (X0 - a.fx);
+    if (roi[0] && roi[3]) {
+        if (a.plane_c) *(float4*)(a.plane_c + po) = make_float4(cval[0], cval[1], cval[2], cval[3]);
+        *(float4*)(a.plane_dc + po) = make_float4(dcv[0], dcv[1], dcv[2], dcv[3]);
+    } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            if (roi[q]) { if (a.plane_c) a.plane_c[po + q] = cval[q]; a.plane_dc[po + q] = dcv[q]; }
+    }
 }
 
 // ---- standalone FGS: interleaved source -> float planes, float planes -> interleaved dst ------

@@ -33,7 +33,11 @@ out = torch.empty((B, H, W), dtype=torch.int16, device=dev); conf = torch.empty(
 bf = BatchFilter(True, 8000.0, 1.5, 24, 3, ctx=ctx)
 roi = (83, 3, 874, 534)
 ms = timeit(lambda: bf.filter_device(tl, tv, out, tr, conf, roi))
-res["cfg4_half_res_1080p"] = {"ms_per_step": ms, "frames": B, "Mpix_per_s": B * W * H / ms / 1e3}
+ctx.kernel_timing_report(); ctx.set_kernel_timing(True)
+for _ in range(5): bf.filter_device(tl, tv, out, tr, conf, roi)
+kt = ctx.kernel_timing_report(); ctx.set_kernel_timing(False)
+res["cfg4_half_res_1080p"] = {"ms_per_step": ms, "frames": B, "Mpix_per_s": B * W * H / ms / 1e3,
+                              "kernels_us_per_frame": {k: round(t / 5 / B * 1e3, 2) for k, (n, t) in kt.items()}}
 
 # ---- cfg3: FGS standalone 4K through dwls_fgs_dev ----
 W, H = 3840, 2160
