@@ -7,6 +7,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -31,6 +32,16 @@ struct dwls_ctx {
     struct Span { int id; cudaEvent_t a, b; };
     std::vector<Span> spans;
     std::vector<cudaEvent_t> free_events;
+    // CUDA-graph cache of whole filter_frames() launch sequences, keyed by every argument that reaches a kernel.
+    // A sequence is captured the second time its key is seen (callers that pass fresh buffers every call never pay
+    // for a capture) and replayed as one graph launch afterwards.
+    bool graphs = true;
+    cudaStream_t cap_stream = nullptr;
+    struct GraphEntry { std::string key; cudaGraphExec_t exec; int64_t kernels; uint64_t last_use; };
+    std::vector<GraphEntry> graph_cache;
+    std::vector<size_t> seen_once;
+    uint64_t graph_clock = 0;
+    int64_t graph_replays = 0;
 };
 
 enum KernelId { K_LUT = 0, K_WEIGHTS, K_CONF_R, K_CONF_L, K_UPSCALE, K_PREP, K_FILL, K_HSOLVE, K_VSOLVE, K_VSOLVE_FIN, K_UNPACK, K_PACK, K_COUNT };
@@ -77,7 +88,12 @@ static inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 static dwls_status ensure(dwls_ctx* ctx, void** p, size_t* have, size_t need)
 {
     if (*have >= need) return DWLS_OK;
-    if (*p) { CK(cudaStreamSynchronize(ctx->stream)); CK(cudaFree(*p)); *p = nullptr; *have = 0; }
+    if (*p) {
+        CK(cudaDeviceSynchronize());
+        for (auto& ge : ctx->graph_cache) cudaGraphExecDestroy(ge.exec);      // cached graphs point into the old allocation
+        ctx->graph_cache.clear();
+        CK(cudaFree(*p)); *p = nullptr; *have = 0;
+    }
     CK(cudaMalloc(p, need));
     *have = need;
     return DWLS_OK;
@@ -124,6 +140,8 @@ void dwls_ctx_destroy(dwls_ctx* ctx)
     cudaSetDevice(ctx->device);
     if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
     if (ctx->stream2) { cudaStreamSynchronize(ctx->stream2); cudaStreamDestroy(ctx->stream2); }
+    for (auto& ge : ctx->graph_cache) cudaGraphExecDestroy(ge.exec);
+    if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
     cudaFree(ctx->lut); cudaFree(ctx->ws); cudaFree(ctx->stage);
     for (auto& sp : ctx->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto e : ctx->free_events) cudaEventDestroy(e);
@@ -138,6 +156,14 @@ dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames)
     ctx->group_frames = frames;
     return DWLS_OK;
 }
+
+dwls_status dwls_set_cuda_graphs(dwls_ctx* ctx, int on)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    ctx->graphs = on != 0;
+    return DWLS_OK;
+}
+int64_t dwls_graph_replays(const dwls_ctx* ctx) { return ctx ? ctx->graph_replays : 0; }
 
 dwls_status dwls_set_kernel_timing(dwls_ctx* ctx, int on)
 {
@@ -570,6 +596,75 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
     return run_sweeps(ctx, a, chor, cvert, conf ? 2 : 1, conf ? FIN_WLS : FIN_S16, g.plan, nf, p->lambda, p->lambda_attenuation, p->num_iter, st);
 }
 
+// filter_frames() through the graph cache: same launches, one cudaGraphLaunch once the sequence has been seen twice.
+// Workspace and LUT must already be in place (no allocation happens inside a capture).
+static dwls_status filter_frames_graphed(dwls_ctx* ctx, const dwls_batch* b, int f0, int nf, const Geom& g, const dwls_params* p,
+                                         const int* roi_in, cudaStream_t st, float* ws_base = nullptr)
+{
+    if (!ctx->graphs || ctx->timing) return filter_frames(ctx, b, f0, nf, g, p, nullptr, 0, false, st, ws_base);
+    std::string key;
+    auto put = [&key](const void* v, size_t n) { key.append((const char*)v, n); };
+#define PUT(x) put(&(x), sizeof(x))
+    PUT(b->disp_left); PUT(b->dl_step); PUT(b->dl_frame); PUT(b->disp_right); PUT(b->dr_step); PUT(b->dr_frame);
+    PUT(b->disp_cols); PUT(b->disp_rows); PUT(b->view); PUT(b->view_step); PUT(b->view_frame); PUT(b->view_cols); PUT(b->view_rows);
+    PUT(b->view_channels); PUT(b->out); PUT(b->out_step); PUT(b->out_frame); PUT(b->conf); PUT(b->conf_step); PUT(b->conf_frame);
+    PUT(f0); PUT(nf);
+    PUT(p->lambda); PUT(p->sigma_color); PUT(p->lrc_thresh); PUT(p->disc_radius); PUT(p->left_offset); PUT(p->right_offset);
+    PUT(p->top_offset); PUT(p->bottom_offset); PUT(p->use_confidence); PUT(p->lambda_attenuation); PUT(p->num_iter);
+    const int no_roi[4] = { -1, -1, -1, -1 };
+    put(roi_in ? roi_in : no_roi, sizeof no_roi);
+    float* base = ws_base ? ws_base : (float*)ctx->ws;
+    PUT(base); PUT(ctx->lut);
+#undef PUT
+    for (auto& ge : ctx->graph_cache)
+        if (ge.key == key) {
+            ge.last_use = ++ctx->graph_clock;
+            CK(cudaGraphLaunch(ge.exec, st));
+            ctx->launches += ge.kernels;
+            ctx->graph_replays++;
+            return DWLS_OK;
+        }
+    const size_t h = std::hash<std::string>()(key);
+    bool seen = false;
+    for (size_t v : ctx->seen_once) seen |= (v == h);
+    if (!seen) {
+        if (ctx->seen_once.size() >= 64) ctx->seen_once.erase(ctx->seen_once.begin());
+        ctx->seen_once.push_back(h);
+        return filter_frames(ctx, b, f0, nf, g, p, nullptr, 0, false, st, ws_base);
+    }
+    // capture on a private stream (the caller's may be the legacy default stream, which cannot be captured)
+    if (!ctx->cap_stream) CK(cudaStreamCreateWithFlags(&ctx->cap_stream, cudaStreamNonBlocking));
+    const int64_t before = ctx->launches;
+    CK(cudaStreamBeginCapture(ctx->cap_stream, cudaStreamCaptureModeThreadLocal));
+    const dwls_status s = filter_frames(ctx, b, f0, nf, g, p, nullptr, 0, false, ctx->cap_stream, ws_base);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(ctx->cap_stream, &graph);
+    const int64_t kernels = ctx->launches - before;
+    ctx->launches = before;
+    if (s) { if (graph) cudaGraphDestroy(graph); return s; }
+    if (ce != cudaSuccess || !graph) {                      // capture refused: run the plain launches instead
+        cudaGetLastError();
+        if (graph) cudaGraphDestroy(graph);
+        return filter_frames(ctx, b, f0, nf, g, p, nullptr, 0, false, st, ws_base);
+    }
+    cudaGraphExec_t exec = nullptr;
+    const cudaError_t ie = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ie != cudaSuccess) { cudaGetLastError(); return filter_frames(ctx, b, f0, nf, g, p, nullptr, 0, false, st, ws_base); }
+    if (ctx->graph_cache.size() >= 16) {
+        size_t lru = 0;
+        for (size_t i = 1; i < ctx->graph_cache.size(); ++i) if (ctx->graph_cache[i].last_use < ctx->graph_cache[lru].last_use) lru = i;
+        // the evicted graph may still be running: the runtime defers the release until it has finished
+        cudaGraphExecDestroy(ctx->graph_cache[lru].exec);
+        ctx->graph_cache.erase(ctx->graph_cache.begin() + lru);
+    }
+    ctx->graph_cache.push_back({ key, exec, kernels, ++ctx->graph_clock });
+    CK(cudaGraphLaunch(exec, st));
+    ctx->launches += kernels;
+    ctx->graph_replays++;
+    return DWLS_OK;
+}
+
 static int pick_group(const dwls_ctx* ctx, size_t per_frame_bytes, int n)
 {
     if (ctx->group_frames > 0) return ctx->group_frames < n ? ctx->group_frames : n;
@@ -617,7 +712,7 @@ extern "C" dwls_status dwls_filter_batch_dev(dwls_ctx* ctx, const dwls_batch* b,
     if ((s = ensure_lut(ctx, (float)p->sigma_color, st))) return s;
     for (int f0 = 0; f0 < b->n_frames; f0 += G) {
         const int nf = (b->n_frames - f0 < G) ? b->n_frames - f0 : G;
-        if ((s = filter_frames(ctx, b, f0, nf, g, p, nullptr, 0, false, st))) return s;
+        if ((s = filter_frames_graphed(ctx, b, f0, nf, g, p, roi_in, st))) return s;
     }
     return DWLS_OK;
 }
@@ -692,7 +787,7 @@ static dwls_status filter_host_impl(dwls_ctx* ctx, const dwls_image* dl, const d
         return DWLS_OK;
     }
     if ((s = ensure_lut(ctx, (float)p->sigma_color, st))) return s;
-    if ((s = filter_frames(ctx, &b, 0, 1, g, p, nullptr, 0, false, st))) return s;
+    if ((s = filter_frames_graphed(ctx, &b, 0, 1, g, p, roi_in, st))) return s;
     CK(cudaMemcpy2DAsync(out->data, out->step, d_out, (size_t)W * 2, (size_t)W * 2, H, cudaMemcpyDeviceToHost, st));
     if (want_conf) CK(cudaMemcpy2DAsync(conf->data, conf->step, d_conf, (size_t)W * 4, (size_t)W * 4, H, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));

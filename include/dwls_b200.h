@@ -81,6 +81,11 @@ DWLS_API int64_t     dwls_kernel_launches(const dwls_ctx* ctx);
  * the device, returns one entry per kernel that ran since the last report and resets the record. */
 DWLS_API dwls_status dwls_set_kernel_timing(dwls_ctx* ctx, int on);
 DWLS_API int         dwls_kernel_timing_report(dwls_ctx* ctx, const char** names, int64_t* launches, double* total_ms, int cap);
+/* CUDA-graph replay of a filter call's launch sequence (on by default).  A sequence is captured the second time
+ * the same buffers, geometry and parameters are passed and replayed as one graph launch from then on; kernels counted
+ * by dwls_kernel_launches include the replayed ones.  Timing mode always uses plain launches. */
+DWLS_API dwls_status dwls_set_cuda_graphs(dwls_ctx* ctx, int on);
+DWLS_API int64_t     dwls_graph_replays(const dwls_ctx* ctx);
 /* frames processed per kernel launch group in the batch entry point (0 = choose automatically) */
 DWLS_API dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames);
 

@@ -4,6 +4,7 @@ frame by frame: independent frames of a batch must come out exactly as single fi
 import numpy as np
 import pytest
 
+import addingdisparityfiltering_b200 as A
 from addingdisparityfiltering_b200 import synth
 from addingdisparityfiltering_b200.batch import BatchFilter
 from oracle import oracle as O
@@ -97,3 +98,55 @@ def test_batch_half_res_device(ctx):
         ref = O.wls_filter(dl2[i], view[i], dr2[i], roi=roi, lam=8000.0, sigma=1.5, lrc_thresh=24, disc_radius=3)
         assert np.abs(conf[i].cpu().numpy() - ref["conf"]).max() <= 1e-4
         assert_s16_parity(out[i].cpu().numpy(), ref["out"], froi)
+
+
+@pytest.mark.gpu
+def test_graph_replay_matches_plain_launches():
+    """Third and later calls with the same buffers replay a captured CUDA graph: results and kernel counts are unchanged,
+    and changing an argument (lambda, ROI) never replays a stale graph."""
+    import torch
+    dev = torch.device("cuda", 0)
+    ctx = A.Context(0)
+    frames = [synth.make_artificial_example(320, 240, 3, seed=40 + i) for i in range(3)]
+    roi = frames[0][3]
+    view = torch.from_numpy(np.stack([f[0] for f in frames])).to(dev)
+    dl = torch.from_numpy(np.stack([f[1] for f in frames])).to(dev)
+    dr = torch.from_numpy(np.stack([f[2] for f in frames])).to(dev)
+    out = torch.empty((3, 240, 320), dtype=torch.int16, device=dev)
+    conf = torch.empty((3, 240, 320), dtype=torch.float32, device=dev)
+    bf = BatchFilter(True, 8000.0, 1.5, 24, 2, ctx=ctx)
+    ctx.set_cuda_graphs(False)
+    bf.filter_device(dl, view, out, dr, conf, roi)          # builds the LUT for this sigma once
+    n0 = ctx.kernel_launches()
+    bf.filter_device(dl, view, out, dr, conf, roi)
+    torch.cuda.synchronize()
+    per_call = ctx.kernel_launches() - n0
+    ref_out, ref_conf = out.clone(), conf.clone()
+    ctx.set_cuda_graphs(True)
+    for i in range(4):
+        out.fill_(7); conf.fill_(-1)
+        n0 = ctx.kernel_launches()
+        bf.filter_device(dl, view, out, dr, conf, roi)
+        torch.cuda.synchronize()
+        assert ctx.kernel_launches() - n0 == per_call
+        assert torch.equal(out, ref_out) and torch.equal(conf, ref_conf), i
+    assert ctx.graph_replays() >= 2
+    # a changed parameter is a different key
+    bf2 = BatchFilter(True, 2000.0, 1.5, 24, 2, ctx=ctx)
+    ctx.set_cuda_graphs(False)
+    bf2.filter_device(dl, view, out, dr, conf, roi)
+    torch.cuda.synchronize()
+    want = out.clone()
+    ctx.set_cuda_graphs(True)
+    for _ in range(3):
+        out.fill_(7)
+        bf2.filter_device(dl, view, out, dr, conf, roi)
+        torch.cuda.synchronize()
+        assert torch.equal(out, want)
+    assert not torch.equal(want, ref_out)
+    # and the single-frame host entry point goes through the same cache
+    f = A.createDisparityWLSFilterGeneric(True, ctx=ctx)
+    f.setSigmaColor(1.5); f.setDepthDiscontinuityRadius(2)
+    outs = [f.filter(frames[0][1], frames[0][0], None, frames[0][2], roi).copy() for _ in range(4)]
+    assert all((o == outs[0]).all() for o in outs)
+    assert (outs[0] == ref_out[0].cpu().numpy()).all()
