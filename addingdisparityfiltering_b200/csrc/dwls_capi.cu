@@ -210,7 +210,7 @@ static dwls_status ensure_lut(dwls_ctx* ctx, float sigma, cudaStream_t st)
     return DWLS_OK;
 }
 
-struct SolvePlan { int hK, hM; int vM, vCols, vK; };
+struct SolvePlan { int hK, hM; int vM, vCols, vK; int wstrip; };   // wstrip: columns per strip of the strip-major Cvert plane, 0 = row-major
 
 static bool plan_solver(int w, int h, SolvePlan* p)
 {
@@ -221,6 +221,7 @@ static bool plan_solver(int w, int h, SolvePlan* p)
     else if (h <= 17 * 128) { p->vM = 17; p->vCols = 4; }
     else return false;
     p->vK = round_up((h + p->vM - 1) / p->vM, 32);
+    p->wstrip = (p->vM == 9) ? 8 : 0;       // taller images mix 8- and 4-column strips over the same weights: keep them row-major
     return true;
 }
 
@@ -284,7 +285,7 @@ static dwls_status make_tmap(dwls_ctx* ctx, CUtensorMap* tm, const float* base, 
     return DWLS_OK;
 }
 
-template <int M, int S, int VC, int FIN, int MAXT>
+template <int M, int S, int VC, int FIN, int MAXT, bool WB>
 static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
     VTma g;
@@ -294,12 +295,13 @@ static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
     g.strips_total = g.strips_x * frames;
     const size_t smem = vsolve_smem_bytes<M, S, VC>(pl.vK, g.nb * g.rb);
     if (smem > 227 * 1024) return fail(ctx, DWLS_UNSUPPORTED, "image too tall for the shared-memory stage of the column pass");
-    auto k = vsolve_kernel<M, S, VC, FIN, MAXT>;
+    auto k = vsolve_kernel<M, S, VC, FIN, MAXT, WB>;
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CUtensorMap tw, t0, t1;
     dwls_status s;
     const int64_t rows = (int64_t)frames * a.h;           // frames are contiguous planes: a.p_frame == a.w_frame == pitch * h
-    if ((s = make_tmap(ctx, &tw, a.weight, a.pitch, rows, VC, g.rb))) return s;
+    if (WB) tw = CUtensorMap();
+    else if ((s = make_tmap(ctx, &tw, a.weight, a.pitch, rows, VC, g.rb))) return s;
     if ((s = make_tmap(ctx, &t0, a.in[0], a.pitch, rows, VC, g.rb))) return s;
     if (S > 1) { if ((s = make_tmap(ctx, &t1, a.in[1], a.pitch, rows, VC, g.rb))) return s; }
     else t1 = t0;
@@ -316,10 +318,11 @@ static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
 template <int S, int FIN>
 static dwls_status launch_v(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
-    if (pl.vM == 9) return launch_v_inst<9, S, 8, FIN, 1024>(ctx, a, pl, frames, st);
+    if (pl.vM == 9) return pl.wstrip == 8 ? launch_v_inst<9, S, 8, FIN, 1024, true>(ctx, a, pl, frames, st)
+                                          : launch_v_inst<9, S, 8, FIN, 1024, false>(ctx, a, pl, frames, st);
     // 1153..2176 rows, 17 rows per thread: a single plane still fits 8-column strips (32-byte rows) in 64 registers
-    if (pl.vCols == 4 && S == 1) return launch_v_inst<17, 1, 8, FIN == FIN_WLS ? FIN_FLOAT : FIN, 1024>(ctx, a, pl, frames, st);
-    if (pl.vCols == 4) return launch_v_inst<17, S, 4, FIN, 512>(ctx, a, pl, frames, st);
+    if (pl.vCols == 4 && S == 1) return launch_v_inst<17, 1, 8, FIN == FIN_WLS ? FIN_FLOAT : FIN, 1024, false>(ctx, a, pl, frames, st);
+    if (pl.vCols == 4) return launch_v_inst<17, S, 4, FIN, 512, false>(ctx, a, pl, frames, st);
     return fail(ctx, DWLS_UNSUPPORTED, "column pass supports at most 2176 rows");
 }
 
@@ -347,8 +350,9 @@ static dwls_status run_sweeps(dwls_ctx* ctx, SolveArgs a, const float* chor, con
 }
 
 static dwls_status launch_weights(dwls_ctx* ctx, const uint8_t* guide, int64_t gstep, int64_t gframe, int cn, int w, int h,
-                                  int pitch, float* chor, float* cvert, int64_t wframe, int frames, cudaStream_t st)
+                                  int pitch, float* chor, float* cvert, int64_t wframe, int frames, cudaStream_t st, int vstrip)
 {
+    if (vstrip <= 0) vstrip = pitch;
     // threads per CTA: spread the row over equally wide tiles of at most 1024 pixels
     const int tiles = (pitch + 1023) / 1024;
     const int nt = round_up((pitch + 4 * tiles - 1) / (4 * tiles), 32);
@@ -356,8 +360,8 @@ static dwls_status launch_weights(dwls_ctx* ctx, const uint8_t* guide, int64_t g
     const size_t smem = (size_t)(WT_RB + 1) * rowpitch + 8;
     dim3 grid((pitch + 4 * nt - 1) / (4 * nt), (h + WT_RB - 1) / WT_RB, frames);
     KTimer kt_(ctx, K_WEIGHTS, st);
-    if (cn == 1) weights_kernel<1><<<grid, nt, smem, st>>>(guide, gstep, gframe, w, h, pitch, rowpitch, ctx->lut, chor, cvert, wframe);
-    else weights_kernel<3><<<grid, nt, smem, st>>>(guide, gstep, gframe, w, h, pitch, rowpitch, ctx->lut, chor, cvert, wframe);
+    if (cn == 1) weights_kernel<1><<<grid, nt, smem, st>>>(guide, gstep, gframe, w, h, pitch, rowpitch, ctx->lut, chor, cvert, wframe, vstrip);
+    else weights_kernel<3><<<grid, nt, smem, st>>>(guide, gstep, gframe, w, h, pitch, rowpitch, ctx->lut, chor, cvert, wframe, vstrip);
     CK(cudaGetLastError());
     return DWLS_OK;
 }
@@ -586,7 +590,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
         if (bs) return bs;
     }
     dwls_status s = launch_weights(ctx, view + (size_t)g.fy * b->view_step + (size_t)g.fx * g.vcn, b->view_step, b->view_frame, g.vcn,
-                                   g.fw, g.fh, g.pitch, chor, cvert, L.plane, nf, st);
+                                   g.fw, g.fh, g.pitch, chor, cvert, L.plane, nf, st, g.plan.wstrip);
     if (s) return s;
     SolveArgs a;
     memset(&a, 0, sizeof a);
@@ -851,7 +855,7 @@ static dwls_status fgs_dev_impl(dwls_ctx* ctx, const dwls_image* guide, const dw
     if ((s = ensure(ctx, &ctx->ws, &ctx->ws_bytes, align256((2 + S) * plane * sizeof(float))))) return s;
     if ((s = ensure_lut(ctx, (float)sigma, st))) return s;
     float* chor = (float*)ctx->ws; float* cvert = chor + plane; float* planes = cvert + plane;
-    if ((s = launch_weights(ctx, (const uint8_t*)guide->data, guide->step, 0, guide->channels, w, h, pitch, chor, cvert, plane, 1, st))) return s;
+    if ((s = launch_weights(ctx, (const uint8_t*)guide->data, guide->step, 0, guide->channels, w, h, pitch, chor, cvert, plane, 1, st, chor_out ? 0 : pl.wstrip))) return s;   // the exported planes are row-major
     if (chor_out) {
         CK(cudaMemcpy2DAsync(chor_out, (size_t)w * 4, chor, (size_t)pitch * 4, (size_t)w * 4, h, cudaMemcpyDeviceToDevice, st));
         CK(cudaMemcpy2DAsync(cvert_out, (size_t)w * 4, cvert, (size_t)pitch * 4, (size_t)w * 4, h, cudaMemcpyDeviceToDevice, st));

@@ -251,7 +251,9 @@ __host__ __device__ inline size_t vsolve_smem_bytes(int K, int rows_staged)
     return sizeof(float) * ((size_t)(1 + S) * rows_staged * VC + (size_t)VC * (4 + 2 * S) * l2pad_size(K) + (size_t)VC * 32 * (2 + S) * M) + 16;
 }
 
-template <int M, int S, int VC, int FIN, int MAXT>
+// WB: the weight plane is strip-major ([strip][row][VC], written so by weights_kernel) and a strip arrives with one bulk
+// copy; otherwise it is row-major like the data planes and arrives as TMA boxes.
+template <int M, int S, int VC, int FIN, int MAXT, bool WB>
 __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const VTma g, const __grid_constant__ CUtensorMap tm_w,
                                                       const __grid_constant__ CUtensorMap tm_p0, const __grid_constant__ CUtensorMap tm_p1)
 {
@@ -267,14 +269,15 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
     float* A = l2base + x * SYS; float* B = A + KP; float* Bd = B + KP; float* C = Bd + KP;
     float* F = C + KP; float* Fd = F + S * KP;
     const int n_mine = (g.strips_total - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
-    const uint32_t tx_bytes = (uint32_t)((1 + S) * rows_staged * VC * sizeof(float));
+    const uint32_t tx_bytes = (uint32_t)(((WB ? a.h : rows_staged) + S * rows_staged) * VC * sizeof(float));
 
     auto issue = [&](int i) {                                     // thread 0: fetch my i-th strip
         const int si = blockIdx.x + i * gridDim.x, frame = si / g.strips_x, col0 = (si - frame * g.strips_x) * VC;
         mbar_arrive_expect_tx(full, tx_bytes);
+        if (WB) bulk_g2s(stage, a.weight + (size_t)frame * a.w_frame + (size_t)(col0 / VC) * ((size_t)a.h * VC), (uint32_t)(a.h * VC * sizeof(float)), full);
         for (int b = 0; b < g.nb; ++b) {
             const int grow = frame * a.h + b * g.rb;
-            tma_load_2d(stage + (size_t)b * g.rb * VC, &tm_w, col0, grow, full);
+            if (!WB) tma_load_2d(stage + (size_t)b * g.rb * VC, &tm_w, col0, grow, full);
             tma_load_2d(stage + (size_t)(rows_staged + b * g.rb) * VC, &tm_p0, col0, grow, full);
             if (S > 1) tma_load_2d(stage + (size_t)(2 * rows_staged + b * g.rb) * VC, &tm_p1, col0, grow, full);
         }

@@ -68,7 +68,7 @@ __device__ __forceinline__ int wt_dist2(uint32_t a, uint32_t b)
 template <int CN>
 __global__ void __launch_bounds__(256) weights_kernel(const uint8_t* __restrict__ guide, int64_t gstep, int64_t gframe,
                                                       int w, int h, int pitch, int rowpitch, const float* __restrict__ lut,
-                                                      float* __restrict__ chor, float* __restrict__ cvert, int64_t wframe)
+                                                      float* __restrict__ chor, float* __restrict__ cvert, int64_t wframe, int vstrip)
 {
     extern __shared__ __align__(128) uint8_t wsm[];
     uint64_t* bar = (uint64_t*)(wsm + (size_t)(WT_RB + 1) * rowpitch);
@@ -92,11 +92,13 @@ __global__ void __launch_bounds__(256) weights_kernel(const uint8_t* __restrict_
     if (j0 >= pitch) return;
     const int rows_out = min(WT_RB, h - i0);
     float* oh = chor + (size_t)frame * wframe + (size_t)i0 * pitch + j0;
-    float* ov = cvert + (size_t)frame * wframe + (size_t)i0 * pitch + j0;
+    // Cvert is stored as strips of `vstrip` columns, each strip contiguous ([strip][row][vstrip]), so that the column pass
+    // fetches a whole strip with one bulk copy; vstrip == pitch is the plain row-major plane
+    float* ov = cvert + (size_t)frame * wframe + (size_t)(j0 / vstrip) * ((size_t)h * vstrip) + (size_t)i0 * vstrip + (j0 % vstrip);
     if (j0 >= w) {
         for (int r = 0; r < rows_out; ++r) {
             *(float4*)(oh + (size_t)r * pitch) = make_float4(0.f, 0.f, 0.f, 0.f);
-            *(float4*)(ov + (size_t)r * pitch) = make_float4(0.f, 0.f, 0.f, 0.f);
+            *(float4*)(ov + (size_t)r * vstrip) = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         return;
     }
@@ -116,7 +118,7 @@ __global__ void __launch_bounds__(256) weights_kernel(const uint8_t* __restrict_
             vo[q] = (vr && q < nv) ? __ldg(lut + wt_dist2(P[q], N[q])) : 0.f;
         }
         *(float4*)(oh + (size_t)r * pitch) = make_float4(ho[0], ho[1], ho[2], ho[3]);
-        *(float4*)(ov + (size_t)r * pitch) = make_float4(vo[0], vo[1], vo[2], vo[3]);
+        *(float4*)(ov + (size_t)r * vstrip) = make_float4(vo[0], vo[1], vo[2], vo[3]);
 #pragma unroll
         for (int q = 0; q < 5; ++q) P[q] = N[q];
     }
