@@ -357,7 +357,7 @@ static dwls_status launch_weights(dwls_ctx* ctx, const uint8_t* guide, int64_t g
     const int tiles = (pitch + 1023) / 1024;
     const int nt = round_up((pitch + 4 * tiles - 1) / (4 * tiles), 32);
     const int rowpitch = weights_row_pitch(nt, cn);
-    const size_t smem = (size_t)(WT_RB + 1) * rowpitch + 8;
+    const size_t smem = (size_t)(WT_RB + 1) * rowpitch + sizeof(float) * WT_LUT + 8;
     dim3 grid((pitch + 4 * nt - 1) / (4 * nt), (h + WT_RB - 1) / WT_RB, frames);
     KTimer kt_(ctx, K_WEIGHTS, st);
     if (cn == 1) weights_kernel<1><<<grid, nt, smem, st>>>(guide, gstep, gframe, w, h, pitch, rowpitch, ctx->lut, chor, cvert, wframe, vstrip);

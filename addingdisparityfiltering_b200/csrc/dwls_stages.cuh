@@ -33,9 +33,10 @@ __global__ void lut_kernel(float* lut, int n, float sigma)
 // with its 4 pixels (+ right neighbour) of the current row in registers: squared colour
 // distances by VABSDIFF4 + IDP.4A, two LUT gathers per pixel, two float4 stores per row.
 // Columns w..pitch-1 are zero-filled.  grid = (ceil(pitch / (4*blockDim.x)), ceil(h / WT_RB), frames)
-// dynamic smem = (WT_RB+1) * rowpitch + 8
+// dynamic smem = (WT_RB+1) * rowpitch + 4 * WT_LUT + 8
 // ---------------------------------------------------------------------------------------------
 constexpr int WT_RB = 8;
+constexpr int WT_LUT = 2048;   // head of the LUT kept in shared memory (squared distances below 2048 are almost all of a natural image)
 __host__ __device__ inline int weights_row_pitch(int nt, int cn) { return ((4 * nt + 1) * cn + 15 + 15) / 16 * 16 + 16; }
 
 // pixels 0..4 of a thread (channels in the low bytes, high bytes zero) from the staged row; off = byte offset of pixel 0
@@ -71,14 +72,19 @@ __global__ void __launch_bounds__(256) weights_kernel(const uint8_t* __restrict_
                                                       float* __restrict__ chor, float* __restrict__ cvert, int64_t wframe, int vstrip)
 {
     extern __shared__ __align__(128) uint8_t wsm[];
-    uint64_t* bar = (uint64_t*)(wsm + (size_t)(WT_RB + 1) * rowpitch);
+    float* slut = (float*)(wsm + (size_t)(WT_RB + 1) * rowpitch);
+    uint64_t* bar = (uint64_t*)(slut + WT_LUT);
     const int tid = threadIdx.x, frame = blockIdx.z, c0 = blockIdx.x * 4 * blockDim.x, i0 = blockIdx.y * WT_RB;
     const int nrows = min(WT_RB + 1, h - i0);                           // guide rows staged
     const int npx = min(4 * (int)blockDim.x + 1, w - c0);               // pixels available from c0 on (incl. the right neighbour)
     const uint8_t* seg0 = guide + (size_t)frame * gframe + (size_t)i0 * gstep + (size_t)c0 * CN;
-    if (tid == 0) { mbar_init(bar, npx > 0 ? nrows : 1); mbar_fence_init(); }
+    if (tid == 0) { mbar_init(bar, npx > 0 ? nrows + 1 : 1); mbar_fence_init(); }
     __syncthreads();
     if (npx > 0) {
+        if (tid == 31) {
+            mbar_arrive_expect_tx(bar, WT_LUT * (uint32_t)sizeof(float));
+            bulk_g2s(slut, lut, WT_LUT * (uint32_t)sizeof(float), bar);
+        }
         if (tid < nrows) {
             const uint8_t* rp = seg0 + (size_t)tid * gstep;
             const int mis = (int)((uintptr_t)rp & 15);
@@ -114,8 +120,9 @@ __global__ void __launch_bounds__(256) weights_kernel(const uint8_t* __restrict_
         float ho[4], vo[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            ho[q] = (q < nh) ? __ldg(lut + wt_dist2(P[q], P[q + 1])) : 0.f;   // Chor[i][w-1] = 0 (614)
-            vo[q] = (vr && q < nv) ? __ldg(lut + wt_dist2(P[q], N[q])) : 0.f;
+            const int dh2 = wt_dist2(P[q], P[q + 1]), dv2 = wt_dist2(P[q], N[q]);
+            ho[q] = (q < nh) ? (dh2 < WT_LUT ? slut[dh2] : __ldg(lut + dh2)) : 0.f;   // Chor[i][w-1] = 0 (614)
+            vo[q] = (vr && q < nv) ? (dv2 < WT_LUT ? slut[dv2] : __ldg(lut + dv2)) : 0.f;
         }
         *(float4*)(oh + (size_t)r * pitch) = make_float4(ho[0], ho[1], ho[2], ho[3]);
         *(float4*)(ov + (size_t)r * vstrip) = make_float4(vo[0], vo[1], vo[2], vo[3]);
