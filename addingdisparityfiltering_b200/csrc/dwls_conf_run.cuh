@@ -210,21 +210,27 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
     // copies into the warp's shared buffer, one row ahead, and land while the sums of the current row are formed.
     // Misses are issued with src-size 0 (zero fill, no global access) so the loop has no branches.
     auto issue_gather = [&](int y, int buf) {
-        const int16_t* crow16 = (const int16_t*)tile + (size_t)(y - ylo) * PITCH + CR_HL + g;
-        const int16_t* drow = a.dr + (size_t)frame * a.dr_frame + (size_t)(a.ry + y) * a.dr_step + a.rrx;
-        const float* crow = a.conf_r + (size_t)frame * a.cr_frame + (size_t)y * a.cr_pitch;
+        // 64-bit row bases once, 32-bit offsets per element (the offsets are bounded by the row length)
+        const uint32_t crow16 = smem_u32((const int16_t*)tile + (size_t)(y - ylo) * PITCH + CR_HL + g);
+        const uint64_t dbase = (uint64_t)(uintptr_t)(a.dr + (size_t)frame * a.dr_frame + (size_t)(a.ry + y) * a.dr_step + a.rrx);
+        const uint64_t dal = dbase & ~(uint64_t)3;                       // the copies fetch the aligned word holding the element
+        const uint32_t dpar = (uint32_t)(dbase >> 1) & 1u;
+        const uint64_t cbase = (uint64_t)(uintptr_t)(a.conf_r + (size_t)frame * a.cr_frame + (size_t)y * a.cr_pitch);
         const int xr = a.rx + tx0 + g - a.rrx;
         const uint32_t cb = smem_u32(capbuf + (band * 2 + buf) * 512 + g);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             const bool in = 32 * k + g < 8 * G;
-            const int L = in ? (int)crow16[32 * k] : 0;
+            int L;
+            asm volatile("ld.shared.s16 %0, [%1];" : "=r"(L) : "r"(crow16 + 2 * 32 * k));
             const int ro = xr + 32 * k - (L >> 4);                                                 // 331, relative to the right ROI
             const bool ok = in && (unsigned)ro < (unsigned)a.rw;                                   // 332
-            const int roc = ok ? ro : 0;
+            const uint32_t roc = ok ? (uint32_t)ro : 0u;
             const uint32_t sz = ok ? 4u : 0u;
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(cb + 4 * (32 * k)), "l"(crow + roc), "r"(sz) : "memory");
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(cb + 4 * (256 + 32 * k)), "l"((uintptr_t)(drow + roc) & ~(uintptr_t)3), "r"(sz) : "memory");
+            const uint64_t ca = cbase + (uint64_t)(roc * 4u);
+            const uint64_t da = dal + (uint64_t)(((roc + dpar) >> 1) * 4u);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(cb + 4 * (32 * k)), "l"(ca), "r"(sz) : "memory");
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(cb + 4 * (256 + 32 * k)), "l"(da), "r"(sz) : "memory");
         }
     };
     if (LEFT) { issue_gather(yb, 0); asm volatile("cp.async.commit_group;" ::: "memory"); }
