@@ -293,7 +293,7 @@ static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
     g.rb = round_up((a.h + g.nb - 1) / g.nb, 128 / (VC * 4));     // every TMA box must land on a 128-byte boundary in smem
     g.strips_x = (a.w + VC - 1) / VC;
     g.strips_total = g.strips_x * frames;
-    const size_t smem = vsolve_smem_bytes<M, S, VC>(pl.vK, g.nb * g.rb);
+    const size_t smem = vsolve_smem_bytes<M, S, VC>(pl.vK, g.nb * g.rb, WB ? 2 : 1);
     if (smem > 227 * 1024) return fail(ctx, DWLS_UNSUPPORTED, "image too tall for the shared-memory stage of the column pass");
     auto k = vsolve_kernel<M, S, VC, FIN, MAXT, WB>;
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -245,14 +245,17 @@ struct VTma {
     int strips_total;  // strips_x * frames
 };
 
+// wbuf: staged copies of the weight strip (1, or 2 when it is double-buffered)
 template <int M, int S, int VC>
-__host__ __device__ inline size_t vsolve_smem_bytes(int K, int rows_staged)
+__host__ __device__ inline size_t vsolve_smem_bytes(int K, int rows_staged, int wbuf)
 {
-    return sizeof(float) * ((size_t)(1 + S) * rows_staged * VC + (size_t)VC * (4 + 2 * S) * l2pad_size(K) + (size_t)VC * 32 * (2 + S) * M) + 16;
+    return sizeof(float) * ((size_t)(wbuf + S) * rows_staged * VC + (size_t)VC * (4 + 2 * S) * l2pad_size(K) + (size_t)VC * 32 * (2 + S) * M) + 32;
 }
 
 // WB: the weight plane is strip-major ([strip][row][VC], written so by weights_kernel) and a strip arrives with one bulk
-// copy; otherwise it is row-major like the data planes and arrives as TMA boxes.
+// copy into one of two buffers, requested a whole strip ahead (the weights are only read by level 1, so their buffer is
+// free again long before the data planes' stage is); otherwise it is row-major like the data planes and arrives as TMA
+// boxes together with them.
 template <int M, int S, int VC, int FIN, int MAXT, bool WB>
 __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const VTma g, const __grid_constant__ CUtensorMap tm_w,
                                                       const __grid_constant__ CUtensorMap tm_p0, const __grid_constant__ CUtensorMap tm_p1)
@@ -261,46 +264,59 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
     const int K = blockDim.x / VC, M2 = K >> 5, KP = l2pad_size(K);
     const int SYS = (4 + 2 * S) * KP;
     const int rows_staged = g.nb * g.rb;
-    float* stage = sm;                                            // [1+S][rows_staged][8]
-    float* l2base = sm + (size_t)(1 + S) * rows_staged * VC;      // [8][SYS]
+    constexpr int NW = WB ? 2 : 1;
+    float* wstage = sm;                                           // [NW][rows_staged][VC]
+    float* stage = sm + (size_t)NW * rows_staged * VC;            // [S][rows_staged][VC]
+    float* l2base = stage + (size_t)S * rows_staged * VC;         // [VC][SYS]
     float* stash = l2base + (size_t)VC * SYS;                      // [(2+S)*M][32*VC]: level-2 warps park their level-1 state
     uint64_t* full = (uint64_t*)(stash + (size_t)VC * 32 * (2 + S) * M);
+    uint64_t* wfull = full + 1;                                   // [2]
     const int t = threadIdx.x, x = t % VC, k = t / VC, r0 = k * M;
     float* A = l2base + x * SYS; float* B = A + KP; float* Bd = B + KP; float* C = Bd + KP;
     float* F = C + KP; float* Fd = F + S * KP;
     const int n_mine = (g.strips_total - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
-    const uint32_t tx_bytes = (uint32_t)(((WB ? a.h : rows_staged) + S * rows_staged) * VC * sizeof(float));
+    const uint32_t tx_bytes = (uint32_t)(((WB ? 0 : rows_staged) + S * rows_staged) * VC * sizeof(float));
 
-    auto issue = [&](int i) {                                     // thread 0: fetch my i-th strip
+    auto issue = [&](int i) {                                     // thread 0: fetch the data planes of my i-th strip
         const int si = blockIdx.x + i * gridDim.x, frame = si / g.strips_x, col0 = (si - frame * g.strips_x) * VC;
         mbar_arrive_expect_tx(full, tx_bytes);
-        if (WB) bulk_g2s(stage, a.weight + (size_t)frame * a.w_frame + (size_t)(col0 / VC) * ((size_t)a.h * VC), (uint32_t)(a.h * VC * sizeof(float)), full);
         for (int b = 0; b < g.nb; ++b) {
             const int grow = frame * a.h + b * g.rb;
-            if (!WB) tma_load_2d(stage + (size_t)b * g.rb * VC, &tm_w, col0, grow, full);
-            tma_load_2d(stage + (size_t)(rows_staged + b * g.rb) * VC, &tm_p0, col0, grow, full);
-            if (S > 1) tma_load_2d(stage + (size_t)(2 * rows_staged + b * g.rb) * VC, &tm_p1, col0, grow, full);
+            if (!WB) tma_load_2d(wstage + (size_t)b * g.rb * VC, &tm_w, col0, grow, full);
+            tma_load_2d(stage + (size_t)(b * g.rb) * VC, &tm_p0, col0, grow, full);
+            if (S > 1) tma_load_2d(stage + (size_t)(rows_staged + b * g.rb) * VC, &tm_p1, col0, grow, full);
         }
     };
+    auto issue_w = [&](int i) {                                   // thread 0: fetch the weight strip of my i-th strip
+        const int si = blockIdx.x + i * gridDim.x, frame = si / g.strips_x, strip = si - frame * g.strips_x;
+        const uint32_t bytes = (uint32_t)(a.h * VC * sizeof(float));
+        mbar_arrive_expect_tx(wfull + (i & 1), bytes);
+        bulk_g2s(wstage + (size_t)(i & 1) * rows_staged * VC, a.weight + (size_t)frame * a.w_frame + (size_t)strip * ((size_t)a.h * VC), bytes, wfull + (i & 1));
+    };
 
-    if (t == 0) { mbar_init(full, 1); mbar_fence_init(); }
+    if (t == 0) { mbar_init(full, 1); mbar_init(wfull, 1); mbar_init(wfull + 1, 1); mbar_fence_init(); }
     __syncthreads();
-    if (t == 0 && n_mine > 0) issue(0);
+    if (t == 0 && n_mine > 0) { if (WB) issue_w(0); issue(0); }
 
     for (int i = 0; i < n_mine; ++i) {
         const int si = blockIdx.x + i * gridDim.x, frame = si / g.strips_x, col = (si - frame * g.strips_x) * VC + x;
         const bool live = col < a.w;
+        if (WB) {
+            if (t == 0 && i + 1 < n_mine) issue_w(i + 1);        // its buffer was last read by level 1 of strip i-1
+            mbar_wait(wfull + (i & 1), (uint32_t)((i >> 1) & 1));
+        }
         mbar_wait(full, (uint32_t)(i & 1));
         float c[M], v[M], f[S][M];
         float aprev = 0.f;
         {
-            const float* sw = stage + (size_t)r0 * VC + x;
+            const float* sw = wstage + (size_t)(WB ? (i & 1) : 0) * rows_staged * VC + (size_t)r0 * VC + x;
+            const float* sp = stage + (size_t)r0 * VC + x;
             if (live && r0 + M < a.h) {                                  // chunk strictly inside the column: no masks
 #pragma unroll
                 for (int m = 0; m < M; ++m) {
                     c[m] = a.lam * sw[m * VC];
 #pragma unroll
-                    for (int s = 0; s < S; ++s) f[s][m] = sw[(size_t)(1 + s) * rows_staged * VC + m * VC];
+                    for (int s = 0; s < S; ++s) f[s][m] = sp[(size_t)s * rows_staged * VC + m * VC];
                 }
             } else {
 #pragma unroll
@@ -308,7 +324,7 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
                     const bool in = live && (r0 + m < a.h);
                     c[m] = (live && (r0 + m < a.h - 1)) ? a.lam * sw[m * VC] : 0.f;              // last row weight 0 (fgs_filter.cpp:658-660)
 #pragma unroll
-                    for (int s = 0; s < S; ++s) f[s][m] = in ? sw[(size_t)(1 + s) * rows_staged * VC + m * VC] : 0.f;
+                    for (int s = 0; s < S; ++s) f[s][m] = in ? sp[(size_t)s * rows_staged * VC + m * VC] : 0.f;
                 }
             }
             if (live && k > 0 && r0 - 1 < a.h - 1) aprev = a.lam * sw[-VC];
