@@ -44,10 +44,10 @@ struct dwls_ctx {
     int64_t graph_replays = 0;
 };
 
-enum KernelId { K_LUT = 0, K_WEIGHTS, K_CONF_R, K_CONF_L, K_UPSCALE, K_PREP, K_FILL, K_HSOLVE, K_VSOLVE, K_VSOLVE_FIN, K_UNPACK, K_PACK, K_COUNT };
+enum KernelId { K_LUT = 0, K_WEIGHTS, K_CONF_R, K_CONF_L, K_UPSCALE, K_PREP, K_FILL, K_HSOLVE, K_VSOLVE, K_VSOLVE_FIN, K_UNPACK, K_PACK, K_TRANSPOSE, K_COUNT };
 static const char* const kKernelNames[K_COUNT] = { "lut_kernel", "weights_kernel", "conf_kernel<right>", "conf_kernel<left+lrc>", "upscale_prep_kernel",
                                                    "prep_noconf_kernel", "border_kernel", "hsolve_kernel", "vsolve_kernel", "vsolve_kernel<final>",
-                                                   "unpack_kernel", "pack_kernel" };
+                                                   "unpack_kernel", "pack_kernel", "transpose_kernel" };
 
 // counts the launch and, when timing is on, brackets it with CUDA events on the launching stream
 struct KTimer {
@@ -210,15 +210,27 @@ static dwls_status ensure_lut(dwls_ctx* ctx, float sigma, cudaStream_t st)
     return DWLS_OK;
 }
 
-struct SolvePlan { int hK, hM; int vM, vCols, vK; int wstrip; };   // wstrip: columns per strip of the strip-major Cvert plane, 0 = row-major
+// wstrip: columns per strip of the strip-major Cvert plane, 0 = row-major.
+// vT: more than 2176 rows, the column pass runs as a row pass over transposed planes (tM elements per thread, tK threads,
+// tpitch floats per transposed row)
+struct SolvePlan { int hK, hM; int vM, vCols, vK; int wstrip; bool vT; int tK, tM, tpitch; };
+constexpr int MAX_SIDE = 8192;
 
 static bool plan_solver(int w, int h, SolvePlan* p)
 {
     p->hM = w <= 2048 ? 8 : 16;
     p->hK = round_up((w + p->hM - 1) / p->hM, 32);
     if (p->hK > 512) return false;
+    p->vT = false; p->tK = p->tM = p->tpitch = 0;
     if (h <= 9 * 128) { p->vM = 9; p->vCols = 8; }
     else if (h <= 17 * 128) { p->vM = 17; p->vCols = 4; }
+    else if (h <= MAX_SIDE) {
+        p->vT = true; p->vM = 0; p->vCols = 0; p->vK = 0; p->wstrip = 0;
+        p->tM = h <= 2048 ? 8 : 16;
+        p->tK = round_up((h + p->tM - 1) / p->tM, 32);
+        p->tpitch = round_up(h, 8);
+        return true;
+    }
     else return false;
     p->vK = round_up((h + p->vM - 1) / p->vM, 32);
     p->wstrip = (p->vM == 9) ? 8 : 0;       // taller images mix 8- and 4-column strips over the same weights: keep them row-major
@@ -326,10 +338,61 @@ static dwls_status launch_v(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& 
     return fail(ctx, DWLS_UNSUPPORTED, "column pass supports at most 2176 rows");
 }
 
+// scratch of the transposed column pass (plan.vT): Cvert transposed once per call, the S planes every column sweep
+struct TPass { float* cvertT; float* pT[2]; size_t tplane; };
+
+template <int S, int FIN>
+static dwls_status launch_transpose(dwls_ctx* ctx, const TrArgs& t, int frames, cudaStream_t st)
+{
+    TIMED(K_TRANSPOSE, st, transpose_kernel<S, FIN><<<dim3((t.cols + 31) / 32, (t.rows + 31) / 32, frames), 256, 0, st>>>(t));
+    CK(cudaGetLastError());
+    return DWLS_OK;
+}
+
+// Cvert [h][pitch] -> [w][tpitch], once after the weights kernel
+static dwls_status transpose_cvert(dwls_ctx* ctx, const float* cvert, size_t plane, int pitch, int w, int h, const SolvePlan& pl, const TPass& T,
+                                   int frames, cudaStream_t st)
+{
+    TrArgs t;
+    memset(&t, 0, sizeof t);
+    t.in[0] = cvert; t.in_frame = (int64_t)plane; t.in_pitch = pitch;
+    t.out[0] = T.cvertT; t.out_frame = (int64_t)T.tplane; t.out_pitch = pl.tpitch;
+    t.rows = h; t.cols = w;
+    return launch_transpose<1, FIN_FLOAT>(ctx, t, frames, st);
+}
+
+// one column sweep of a tall image: transpose the planes, solve their rows, transpose back (epilogue fused there)
+static dwls_status column_sweep_transposed(dwls_ctx* ctx, const SolveArgs& a, int S, int fin, const SolvePlan& pl, const TPass& T, int frames,
+                                           cudaStream_t st)
+{
+    TrArgs t;
+    memset(&t, 0, sizeof t);
+    for (int s = 0; s < S; ++s) { t.in[s] = a.in[s]; t.out[s] = T.pT[s]; }
+    t.in_frame = a.p_frame; t.in_pitch = a.pitch; t.out_frame = (int64_t)T.tplane; t.out_pitch = pl.tpitch;
+    t.rows = a.h; t.cols = a.w;
+    dwls_status s = (S == 1) ? launch_transpose<1, FIN_FLOAT>(ctx, t, frames, st) : launch_transpose<2, FIN_FLOAT>(ctx, t, frames, st);
+    if (s) return s;
+    SolveArgs r = a;
+    r.weight = T.cvertT; r.w_frame = (int64_t)T.tplane; r.p_frame = (int64_t)T.tplane; r.pitch = pl.tpitch; r.w = a.h; r.h = a.w;
+    for (int k = 0; k < S; ++k) { r.in[k] = T.pT[k]; r.out[k] = T.pT[k]; }
+    SolvePlan rp = pl;
+    rp.hK = pl.tK; rp.hM = pl.tM;
+    if ((s = (S == 1) ? launch_h<1>(ctx, r, rp, frames, st) : launch_h<2>(ctx, r, rp, frames, st))) return s;
+    memset(&t, 0, sizeof t);
+    for (int k = 0; k < S; ++k) { t.in[k] = T.pT[k]; t.out[k] = a.out[k]; }
+    t.in_frame = (int64_t)T.tplane; t.in_pitch = pl.tpitch; t.out_frame = a.p_frame; t.out_pitch = a.pitch;
+    t.rows = a.w; t.cols = a.h;
+    t.out16 = a.out16; t.out16_step = a.out16_step; t.out16_frame = a.out16_frame;
+    if (fin == FIN_WLS) return launch_transpose<2, FIN_WLS>(ctx, t, frames, st);
+    if (fin == FIN_S16) return launch_transpose<1, FIN_S16>(ctx, t, frames, st);
+    return (S == 1) ? launch_transpose<1, FIN_FLOAT>(ctx, t, frames, st) : launch_transpose<2, FIN_FLOAT>(ctx, t, frames, st);
+}
+
 // num_iter x (row pass, column pass, lambda *= attenuation) on S <= 2 planes sharing the weights
 // (fgs_filter.cpp:207-212).  fin != FIN_FLOAT fuses the output conversion into the last column pass.
 static dwls_status run_sweeps(dwls_ctx* ctx, SolveArgs a, const float* chor, const float* cvert, int S, int fin,
-                              const SolvePlan& pl, int frames, double lambda, double att, int num_iter, cudaStream_t st)
+                              const SolvePlan& pl, int frames, double lambda, double att, int num_iter, cudaStream_t st,
+                              const TPass* T = nullptr)
 {
     float lam = (float)lambda;                    // the reference keeps lambda and the attenuation in float (70-71, 146-147)
     const float fatt = (float)att;
@@ -338,9 +401,14 @@ static dwls_status run_sweeps(dwls_ctx* ctx, SolveArgs a, const float* chor, con
         a.weight = chor;
         dwls_status s = (S == 1) ? launch_h<1>(ctx, a, pl, frames, st) : launch_h<2>(ctx, a, pl, frames, st);
         if (s) return s;
+        for (int k = 0; k < S; ++k) a.in[k] = a.out[k];          // only the first row pass may read from elsewhere (direct FGS path)
         a.weight = cvert;
         const bool last = (n == num_iter - 1);
-        if (last && fin == FIN_WLS) s = launch_v<2, FIN_WLS>(ctx, a, pl, frames, st);
+        if (pl.vT) {
+            if (!T) return fail(ctx, DWLS_CUDA_ERROR, "internal: transposed column pass without scratch planes");
+            s = column_sweep_transposed(ctx, a, S, last ? fin : FIN_FLOAT, pl, *T, frames, st);
+        }
+        else if (last && fin == FIN_WLS) s = launch_v<2, FIN_WLS>(ctx, a, pl, frames, st);
         else if (last && fin == FIN_S16) s = launch_v<1, FIN_S16>(ctx, a, pl, frames, st);
         else s = (S == 1) ? launch_v<1, FIN_FLOAT>(ctx, a, pl, frames, st) : launch_v<2, FIN_FLOAT>(ctx, a, pl, frames, st);
         if (s) return s;
@@ -490,7 +558,7 @@ static dwls_status make_geom(dwls_ctx* ctx, int dw, int dh, int W, int H, int vc
             return fail(ctx, DWLS_BAD_SIZE, "upscaled ROI does not fit inside the view");
     }
     g->pitch = round_up(g->fw, 8);
-    if (!plan_solver(g->fw, g->fh, &g->plan)) return fail(ctx, DWLS_UNSUPPORTED, "ROI larger than 8192 x 2176 is not supported by the on-chip solver");
+    if (!plan_solver(g->fw, g->fh, &g->plan)) return fail(ctx, DWLS_UNSUPPORTED, "ROI larger than 8192 x 8192 is not supported by the on-chip solver");
     return DWLS_OK;
 }
 
@@ -504,15 +572,16 @@ static dwls_status check_params(dwls_ctx* ctx, const dwls_params* p)
 }
 
 // per-frame workspace layout (floats): chor | cvert | plane0 | plane1 | conf_r | conf_lo
-struct WsLayout { size_t plane, confr, conflo, per_frame; int cr_pitch; };
+struct WsLayout { size_t plane, confr, conflo, tplane, per_frame; int cr_pitch; };   // tplane: transposed plane (tall ROIs), x3: Cvert + 2 planes
 static WsLayout ws_layout(const Geom& g, bool use_conf)
 {
     WsLayout l;
     l.plane = (size_t)g.pitch * g.fh;
     l.cr_pitch = round_up(g.rw, 8);
     l.confr = use_conf ? (size_t)l.cr_pitch * g.rh : 0;
-    l.conflo = (use_conf && !g.same) ? (size_t)g.dw * g.dh : 0;
-    l.per_frame = 4 * l.plane + l.confr + l.conflo;
+    l.conflo = (use_conf && !g.same) ? (size_t)round_up(g.dw * g.dh, 8) : 0;   // keeps what follows 32-byte aligned
+    l.tplane = g.plan.vT ? (size_t)g.plan.tpitch * g.fw : 0;
+    l.per_frame = 4 * l.plane + l.confr + l.conflo + 3 * l.tplane;
     return l;
 }
 
@@ -525,6 +594,9 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
     float* chor = base; float* cvert = chor + (size_t)nf * L.plane;
     float* p0 = cvert + (size_t)nf * L.plane; float* p1 = p0 + (size_t)nf * L.plane;
     float* confr = p1 + (size_t)nf * L.plane; float* conflo = confr + (size_t)nf * L.confr;
+    TPass T;
+    T.cvertT = conflo + (size_t)nf * L.conflo; T.pT[0] = T.cvertT + (size_t)nf * L.tplane; T.pT[1] = T.pT[0] + (size_t)nf * L.tplane;
+    T.tplane = L.tplane;
 
     const int16_t* dl = (const int16_t*)((const uint8_t*)b->disp_left + (size_t)f0 * b->dl_frame);
     const int16_t* dr = b->disp_right ? (const int16_t*)((const uint8_t*)b->disp_right + (size_t)f0 * b->dr_frame) : nullptr;
@@ -592,12 +664,13 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
     dwls_status s = launch_weights(ctx, view + (size_t)g.fy * b->view_step + (size_t)g.fx * g.vcn, b->view_step, b->view_frame, g.vcn,
                                    g.fw, g.fh, g.pitch, chor, cvert, L.plane, nf, st, g.plan.wstrip);
     if (s) return s;
+    if (g.plan.vT && (s = transpose_cvert(ctx, cvert, L.plane, g.pitch, g.fw, g.fh, g.plan, T, nf, st))) return s;
     SolveArgs a;
     memset(&a, 0, sizeof a);
     a.w_frame = L.plane; a.p_frame = L.plane; a.pitch = g.pitch; a.w = g.fw; a.h = g.fh;
     a.in[0] = p0; a.out[0] = p0; a.in[1] = p1; a.out[1] = p1;
     a.out16 = out + (size_t)g.fy * (b->out_step / 2) + g.fx; a.out16_step = b->out_step / 2; a.out16_frame = b->out_frame / 2;
-    return run_sweeps(ctx, a, chor, cvert, conf ? 2 : 1, conf ? FIN_WLS : FIN_S16, g.plan, nf, p->lambda, p->lambda_attenuation, p->num_iter, st);
+    return run_sweeps(ctx, a, chor, cvert, conf ? 2 : 1, conf ? FIN_WLS : FIN_S16, g.plan, nf, p->lambda, p->lambda_attenuation, p->num_iter, st, &T);
 }
 
 // filter_frames() through the graph cache: same launches, one cudaGraphLaunch once the sequence has been seen twice.
@@ -848,24 +921,34 @@ static dwls_status fgs_dev_impl(dwls_ctx* ctx, const dwls_image* guide, const dw
 {
     const int w = guide->cols, h = guide->rows, pitch = round_up(w, 8);
     SolvePlan pl;
-    if (!plan_solver(w, h, &pl)) return fail(ctx, DWLS_UNSUPPORTED, "images larger than 8192 x 2176 are not supported by the on-chip solver");
+    if (!plan_solver(w, h, &pl)) return fail(ctx, DWLS_UNSUPPORTED, "images larger than 8192 x 8192 are not supported by the on-chip solver");
     const size_t plane = (size_t)pitch * h;
     const int S = src ? src->channels : 0;
     dwls_status s;
-    if ((s = ensure(ctx, &ctx->ws, &ctx->ws_bytes, align256((2 + S) * plane * sizeof(float))))) return s;
+    TPass T;
+    T.tplane = pl.vT ? (size_t)pl.tpitch * w : 0;
+    if ((s = ensure(ctx, &ctx->ws, &ctx->ws_bytes, align256(((2 + S) * plane + 3 * T.tplane) * sizeof(float))))) return s;
     if ((s = ensure_lut(ctx, (float)sigma, st))) return s;
     float* chor = (float*)ctx->ws; float* cvert = chor + plane; float* planes = cvert + plane;
+    T.cvertT = planes + (size_t)S * plane; T.pT[0] = T.cvertT + T.tplane; T.pT[1] = T.pT[0] + T.tplane;
     if ((s = launch_weights(ctx, (const uint8_t*)guide->data, guide->step, 0, guide->channels, w, h, pitch, chor, cvert, plane, 1, st, chor_out ? 0 : pl.wstrip))) return s;   // the exported planes are row-major
     if (chor_out) {
         CK(cudaMemcpy2DAsync(chor_out, (size_t)w * 4, chor, (size_t)pitch * 4, (size_t)w * 4, h, cudaMemcpyDeviceToDevice, st));
         CK(cudaMemcpy2DAsync(cvert_out, (size_t)w * 4, cvert, (size_t)pitch * 4, (size_t)w * 4, h, cudaMemcpyDeviceToDevice, st));
         return DWLS_OK;
     }
-    { KTimer kt_(ctx, K_UNPACK, st);
-    if (src->depth == DWLS_8U) launch_unpack<uint8_t>(src, planes, plane, pitch, st);
-    else if (src->depth == DWLS_16S) launch_unpack<int16_t>(src, planes, plane, pitch, st);
-    else launch_unpack<float>(src, planes, plane, pitch, st); }
+    // CV_32FC1 with dense, 32-byte aligned rows of a multiple of 8 pixels IS a solver plane: the first row pass reads src and
+    // writes dst, every later pass works in place on dst, and no conversion kernels run
+    const bool direct = S == 1 && src->depth == DWLS_32F && pitch == w && src->step == (int64_t)w * 4 && dst->step == (int64_t)w * 4 &&
+                        (((uintptr_t)src->data | (uintptr_t)dst->data) & 31) == 0;
+    if (!direct) {
+        KTimer kt_(ctx, K_UNPACK, st);
+        if (src->depth == DWLS_8U) launch_unpack<uint8_t>(src, planes, plane, pitch, st);
+        else if (src->depth == DWLS_16S) launch_unpack<int16_t>(src, planes, plane, pitch, st);
+        else launch_unpack<float>(src, planes, plane, pitch, st);
+    }
     CK(cudaGetLastError());
+    if (pl.vT && (s = transpose_cvert(ctx, cvert, plane, pitch, w, h, pl, T, 1, st))) return s;
     // channels are independent solves sharing the weights (fgs_filter.cpp:200-221): two planes per launch
     for (int c0 = 0; c0 < S; c0 += 2) {
         const int ns = (S - c0 >= 2) ? 2 : 1;
@@ -873,8 +956,10 @@ static dwls_status fgs_dev_impl(dwls_ctx* ctx, const dwls_image* guide, const dw
         memset(&a, 0, sizeof a);
         a.w_frame = plane; a.p_frame = plane; a.pitch = pitch; a.w = w; a.h = h;
         for (int k = 0; k < ns; ++k) { a.in[k] = planes + (size_t)(c0 + k) * plane; a.out[k] = planes + (size_t)(c0 + k) * plane; }
-        if ((s = run_sweeps(ctx, a, chor, cvert, ns, FIN_FLOAT, pl, 1, lambda, att, num_iter, st))) return s;
+        if (direct) { a.in[0] = (const float*)src->data; a.out[0] = (float*)dst->data; }
+        if ((s = run_sweeps(ctx, a, chor, cvert, ns, FIN_FLOAT, pl, 1, lambda, att, num_iter, st, &T))) return s;
     }
+    if (direct) return DWLS_OK;
     { KTimer kt_(ctx, K_PACK, st);
     if (dst->depth == DWLS_8U) launch_pack<uint8_t>(planes, plane, pitch, dst, st);
     else if (dst->depth == DWLS_16S) launch_pack<int16_t>(planes, plane, pitch, dst, st);

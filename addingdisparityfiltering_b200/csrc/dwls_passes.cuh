@@ -406,4 +406,48 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// tall images (more than 2176 rows): a column no longer fits the shared-memory stage of vsolve_kernel, so the
+// column pass runs as a ROW pass over the transposed planes (hsolve_kernel handles lines of up to 8192 unknowns):
+// transpose -> hsolve -> transpose back, the latter with the same fused epilogues as the last column pass.
+// 32 x 32 tiles through shared memory, both sides coalesced.  in: [rows][in_pitch], out: [cols][out_pitch].
+// grid = (ceil(cols/32), ceil(rows/32), frames), block = 256
+// ---------------------------------------------------------------------------------------------
+struct TrArgs {
+    const float* in[2]; int64_t in_frame; int in_pitch;
+    float* out[2]; int64_t out_frame; int out_pitch;
+    int rows, cols;                                              // of the input
+    int16_t* out16; int64_t out16_step, out16_frame;             // FIN != FIN_FLOAT: [cols][rows] at the ROI origin
+};
+
+template <int S, int FIN>
+__global__ void __launch_bounds__(256) transpose_kernel(const TrArgs a)
+{
+    __shared__ float tile[S][32][33];
+    const int frame = blockIdx.z, c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        const float* I = a.in[s] + (size_t)frame * a.in_frame;
+#pragma unroll
+        for (int k = ty; k < 32; k += 8) {
+            const int r = r0 + k, c = c0 + tx;
+            tile[s][k][tx] = (r < a.rows && c < a.cols) ? I[(size_t)r * a.in_pitch + c] : 0.f;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = ty; k < 32; k += 8) {
+        const int orow = c0 + k, ocol = r0 + tx;                 // output coordinates
+        if (orow >= a.cols || ocol >= a.rows) continue;
+        if (FIN == FIN_FLOAT) {
+#pragma unroll
+            for (int s = 0; s < S; ++s) a.out[s][(size_t)frame * a.out_frame + (size_t)orow * a.out_pitch + ocol] = tile[s][tx][k];
+        } else {
+            const float v = (FIN == FIN_WLS) ? wls_normalise(tile[0][tx][k], tile[S - 1][tx][k]) : tile[0][tx][k];
+            a.out16[(size_t)frame * a.out16_frame + (size_t)orow * a.out16_step + ocol] = cvt_s16(v);
+        }
+    }
+}
+
 }  // namespace dwls

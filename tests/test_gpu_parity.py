@@ -223,11 +223,12 @@ def test_confidence_extreme_values(ctx):
         assert np.abs(f.getConfidenceMap() - ref["conf"]).max() <= 1e-4
 
 
-@pytest.mark.parametrize("size", [(2500, 40), (4096, 33), (3840, 48), (5000, 24), (8192, 16), (64, 2000), (40, 1153), (200, 2176)])
+@pytest.mark.parametrize("size", [(2500, 40), (4096, 33), (3840, 48), (5000, 24), (8192, 16), (64, 2000), (40, 1153), (200, 2176),
+                                  (64, 2177), (37, 3000), (130, 4100), (24, 8192)])
 @pytest.mark.parametrize("planes", [1, 2])
 def test_fgs_wide_and_tall_images(ctx, size, planes):
     # rows wider than 2048 take the 16-elements-per-thread row pass (> 4096: 512 threads, looped level 2);
-    # more than 1152 rows take the 17-rows-per-thread column pass
+    # more than 1152 rows take the 17-rows-per-thread column pass, more than 2176 rows the transposed column pass
     w, h = size
     rng = np.random.default_rng(w + h)
     g = _guide(rng, h, w, 3)
@@ -236,3 +237,25 @@ def test_fgs_wide_and_tall_images(ctx, size, planes):
     got = A.fastGlobalSmootherFilter(g, src, 8000.0, 1.5, ctx=ctx)
     ref = O.fgs_filter(g, src, 8000.0, 1.5)
     assert np.abs(got - ref).max() <= 255 * 1e-3
+
+
+@pytest.mark.parametrize("conf", [True, False])
+def test_wls_tall_roi(ctx, conf):
+    # ROI taller than 2176 rows: column sweeps run over transposed planes, the normalisation is fused into the transpose back
+    w, h = 96, 2500
+    view, dl, dr, roi = synth.make_artificial_example(w, h, 3, seed=3)
+    f = A.createDisparityWLSFilterGeneric(conf, ctx=ctx)
+    f.setSigmaColor(1.5)
+    got = f.filter(dl, view, None, dr if conf else None, roi)
+    ref = O.wls_filter(dl, view, dr if conf else None, roi=roi, lam=8000.0, sigma=1.5, use_confidence=conf)
+    assert ref["rc"] == 0
+    if conf:
+        assert np.abs(f.getConfidenceMap() - ref["conf"]).max() <= 1e-4
+    assert_s16_parity(got, ref["out"], roi)
+
+
+def test_size_limit_is_reported(ctx):
+    g = np.zeros((8, 8200), np.uint8)
+    with pytest.raises(A.DwlsError) as e:
+        A.fastGlobalSmootherFilter(g, g.astype(np.float32), 100.0, 1.0, ctx=ctx)
+    assert e.value.status == 4
