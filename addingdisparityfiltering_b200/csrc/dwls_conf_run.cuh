@@ -210,27 +210,34 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
     // copies into the warp's shared buffer, one row ahead, and land while the sums of the current row are formed.
     // Misses are issued with src-size 0 (zero fill, no global access) so the loop has no branches.
     auto issue_gather = [&](int y, int buf) {
-        // 64-bit row bases once, 32-bit offsets per element (the offsets are bounded by the row length)
-        const uint32_t crow16 = smem_u32((const int16_t*)tile + (size_t)(y - ylo) * PITCH + CR_HL + g);
+        // 64-bit row bases once, 32-bit offsets per element (the offsets are bounded by the row length).  All eight left
+        // disparities are read before the first copy is issued: every shared-memory load that precedes a cp.async costs
+        // three filler instructions (LDS -> LDGSTS hazard), so the copies go out as one uninterrupted run.
+        const int16_t* crow = (const int16_t*)tile + (size_t)(y - ylo) * PITCH + CR_HL + g;
         const uint64_t dbase = (uint64_t)(uintptr_t)(a.dr + (size_t)frame * a.dr_frame + (size_t)(a.ry + y) * a.dr_step + a.rrx);
         const uint64_t dal = dbase & ~(uint64_t)3;                       // the copies fetch the aligned word holding the element
         const uint32_t dpar = (uint32_t)(dbase >> 1) & 1u;
         const uint64_t cbase = (uint64_t)(uintptr_t)(a.conf_r + (size_t)frame * a.cr_frame + (size_t)y * a.cr_pitch);
         const int xr = a.rx + tx0 + g - a.rrx;
         const uint32_t cb = smem_u32(capbuf + (band * 2 + buf) * 512 + g);
+        int L[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) L[k] = crow[32 * k];
+        uint32_t roc[8], sz[8];
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             const bool in = 32 * k + g < 8 * G;
-            int L;
-            asm volatile("ld.shared.s16 %0, [%1];" : "=r"(L) : "r"(crow16 + 2 * 32 * k));
-            const int ro = xr + 32 * k - (L >> 4);                                                 // 331, relative to the right ROI
+            const int ro = xr + 32 * k - (L[k] >> 4);                                              // 331, relative to the right ROI
             const bool ok = in && (unsigned)ro < (unsigned)a.rw;                                   // 332
-            const uint32_t roc = ok ? (uint32_t)ro : 0u;
-            const uint32_t sz = ok ? 4u : 0u;
-            const uint64_t ca = cbase + (uint64_t)(roc * 4u);
-            const uint64_t da = dal + (uint64_t)(((roc + dpar) >> 1) * 4u);
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(cb + 4 * (32 * k)), "l"(ca), "r"(sz) : "memory");
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(cb + 4 * (256 + 32 * k)), "l"(da), "r"(sz) : "memory");
+            roc[k] = ok ? (uint32_t)ro : 0u;
+            sz[k] = ok ? 4u : 0u;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const uint64_t ca = cbase + (uint64_t)(roc[k] * 4u);
+            const uint64_t da = dal + (uint64_t)(((roc[k] + dpar) >> 1) * 4u);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(cb + 4 * (32 * k)), "l"(ca), "r"(sz[k]) : "memory");
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(cb + 4 * (256 + 32 * k)), "l"(da), "r"(sz[k]) : "memory");
         }
     };
     if (LEFT) { issue_gather(yb, 0); asm volatile("cp.async.commit_group;" ::: "memory"); }
