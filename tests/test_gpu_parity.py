@@ -259,3 +259,53 @@ def test_size_limit_is_reported(ctx):
     with pytest.raises(A.DwlsError) as e:
         A.fastGlobalSmootherFilter(g, g.astype(np.float32), 100.0, 1.0, ctx=ctx)
     assert e.value.status == 4
+
+
+@pytest.mark.parametrize("size", [(1, 1), (7, 1), (1, 7), (2, 2), (3, 5), (5, 3), (9, 2), (33, 1), (1, 40)])
+@pytest.mark.parametrize("cn", [1, 3])
+def test_fgs_tiny_images(ctx, size, cn):
+    # degenerate lines: a single row has no vertical neighbour (fgs_filter.cpp:637 would read row 1; the last weight of a
+    # line is 0, 614/658-660), rows narrower than the reference's 4-wide SIMD blocks (316, 393)
+    w, h = size
+    rng = np.random.default_rng(10 * w + h)
+    g = _guide(rng, h, w, cn)
+    src = (rng.random((h, w)) * 255).astype(np.float32)
+    got = A.fastGlobalSmootherFilter(g, src, 900.0, 3.0, ctx=ctx)
+    ref = O.fgs_filter(g, src, 900.0, 3.0)
+    assert got.shape == ref.shape and np.isfinite(got).all()
+    assert np.abs(got - ref).max() <= 255 * 1e-3
+
+
+@pytest.mark.parametrize("roi", [(0, 0, 64, 48), (5, 0, 1, 48), (0, 7, 64, 1), (63, 47, 1, 1), (10, 10, 2, 3)])
+def test_wls_roi_touching_borders_and_slivers(ctx, roi):
+    # ROI equal to the image, one column, one row, one pixel in the corner: the box filter reflects inside the crop
+    # (disparity_filters.cpp:168-174) and every line solve degenerates
+    w, h = 64, 48
+    view, dl, dr, _ = synth.make_artificial_example(w, h, 3, seed=21)
+    f = A.createDisparityWLSFilterGeneric(True, ctx=ctx)
+    f.setDepthDiscontinuityRadius(2)
+    got = f.filter(dl, view, None, dr, roi)
+    ref = O.wls_filter(dl, view, dr, roi=roi, lam=8000.0, sigma=1.0, disc_radius=2, want_mask=True)
+    assert ref["rc"] == 0 and tuple(f.getROI()) == tuple(ref["roi"])
+    assert (f.lrc_mask(dl, dr, ROI=roi) == ref["mask"]).all()
+    assert np.abs(f.getConfidenceMap() - ref["conf"]).max() <= 1e-4
+    assert_s16_parity(got, ref["out"], roi)
+
+
+def test_wls_zero_confidence_everywhere(ctx):
+    # left and right maps disagree at every pixel -> confidence 0 everywhere -> the reference divides 0 by (0 + 1e-43f):
+    # 0 * (1 / 1e-43f) = 0 * inf = NaN -> saturate_cast<short>(NaN) = -32768 (disparity_filters.cpp:295-296)
+    w, h = 96, 40
+    rng = np.random.default_rng(4)
+    view = rng.integers(0, 256, (h, w, 3)).astype(np.uint8)
+    dl = np.full((h, w), 16 * 4, np.int16)
+    dr = np.full((h, w), 16 * 40, np.int16)          # L + R far above the threshold
+    roi = (8, 0, w - 8, h)
+    f = A.createDisparityWLSFilterGeneric(True, ctx=ctx)
+    got = f.filter(dl, view, None, dr, roi)
+    ref = O.wls_filter(dl, view, dr, roi=roi, lam=8000.0, sigma=1.0)
+    x, y, rw, rh = roi
+    hit = ref["conf"][y:y + rh, x:x + rw] == 0
+    assert hit.any()
+    assert (f.getConfidenceMap() == ref["conf"]).all()
+    assert (got == ref["out"]).all(), (np.unique(got), np.unique(ref["out"]))
