@@ -49,7 +49,7 @@ class Batch(C.Structure):
 
 
 EXPORTS = ["dwls_default_params", "dwls_ctx_create", "dwls_ctx_destroy", "dwls_last_error", "dwls_version",
-           "dwls_kernel_launches", "dwls_set_group_frames", "dwls_set_kernel_timing", "dwls_kernel_timing_report", "dwls_set_cuda_graphs", "dwls_graph_replays", "dwls_filter_host", "dwls_filter_batch_dev",
+           "dwls_kernel_launches", "dwls_set_group_frames", "dwls_set_kernel_timing", "dwls_kernel_timing_report", "dwls_set_cuda_graphs", "dwls_graph_replays", "dwls_transfer_bytes", "dwls_filter_host", "dwls_filter_batch_dev",
            "dwls_filter_batch_host", "dwls_fgs_host", "dwls_fgs_dev", "dwls_lrc_mask_host", "dwls_fgs_weights_host"]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -91,6 +91,8 @@ def lib():
             L.dwls_set_cuda_graphs.argtypes = [C.c_void_p, C.c_int]
             L.dwls_graph_replays.restype = C.c_int64
             L.dwls_graph_replays.argtypes = [C.c_void_p]
+            L.dwls_transfer_bytes.restype = None
+            L.dwls_transfer_bytes.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
             _lib = L
     return _lib
 
@@ -147,6 +149,12 @@ class Context:
 
     def graph_replays(self):
         return int(lib().dwls_graph_replays(self._h))
+
+    def transfer_bytes(self):
+        """(host->device, device->host) bytes moved by the host-buffer entry points since the context was created."""
+        a, b = C.c_int64(), C.c_int64()
+        lib().dwls_transfer_bytes(self._h, C.byref(a), C.byref(b))
+        return int(a.value), int(b.value)
 
     def set_kernel_timing(self, on):
         self.check(lib().dwls_set_kernel_timing(self._h, int(bool(on))))

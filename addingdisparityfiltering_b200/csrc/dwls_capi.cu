@@ -23,6 +23,7 @@ struct dwls_ctx {
     cudaStream_t stream2 = nullptr;                         // second lane of the pipelined host-batch entry point
     std::string err;
     int64_t launches = 0;
+    int64_t h2d_bytes = 0, d2h_bytes = 0;                   // moved by the host-buffer entry points
     int group_frames = 0;
     float* lut = nullptr; float lut_sigma = -1.f;           // per-sigma LUT cache (fgs_filter.cpp:150-154)
     void* ws = nullptr; size_t ws_bytes = 0;                // solver workspace (grow-only)
@@ -164,6 +165,11 @@ dwls_status dwls_set_cuda_graphs(dwls_ctx* ctx, int on)
     return DWLS_OK;
 }
 int64_t dwls_graph_replays(const dwls_ctx* ctx) { return ctx ? ctx->graph_replays : 0; }
+void dwls_transfer_bytes(const dwls_ctx* ctx, int64_t* h2d, int64_t* d2h)
+{
+    if (h2d) *h2d = ctx ? ctx->h2d_bytes : 0;
+    if (d2h) *d2h = ctx ? ctx->d2h_bytes : 0;
+}
 
 dwls_status dwls_set_kernel_timing(dwls_ctx* ctx, int on)
 {
@@ -842,6 +848,8 @@ static dwls_status filter_host_impl(dwls_ctx* ctx, const dwls_image* dl, const d
     uint8_t* d = (uint8_t*)ctx->stage;
     uint8_t* d_dl = d; uint8_t* d_dr = d_dl + b_dl; uint8_t* d_view = d_dr + b_dl; uint8_t* d_out = d_view + b_view;
     uint8_t* d_conf = d_out + b_out; uint8_t* d_mask = d_conf + b_conf;
+    ctx->h2d_bytes += (int64_t)dw * dh * 2 * (useconf ? 2 : 1) + (mask_only ? 0 : (int64_t)W * H * vcn);
+    ctx->d2h_bytes += mask_only ? (int64_t)dw * dh : (int64_t)W * H * 2 + (want_conf ? (int64_t)W * H * 4 : 0);
     CK(cudaMemcpy2DAsync(d_dl, (size_t)dw * 2, dl->data, dl->step, (size_t)dw * 2, dh, cudaMemcpyHostToDevice, st));
     if (useconf) CK(cudaMemcpy2DAsync(d_dr, (size_t)dw * 2, dr->data, dr->step, (size_t)dw * 2, dh, cudaMemcpyHostToDevice, st));
     if (!mask_only) CK(cudaMemcpy2DAsync(d_view, (size_t)W * vcn, view->data, view->step, (size_t)W * vcn, H, cudaMemcpyHostToDevice, st));
@@ -991,6 +999,8 @@ extern "C" dwls_status dwls_fgs_host(dwls_ctx* ctx, const dwls_image* guide, con
     const size_t b_g = align256(grow * h), b_s = align256(srow * h);
     if ((s = ensure(ctx, &ctx->stage, &ctx->stage_bytes, b_g + 2 * b_s))) return s;
     uint8_t* d_g = (uint8_t*)ctx->stage; uint8_t* d_s = d_g + b_g; uint8_t* d_d = d_s + b_s;
+    ctx->h2d_bytes += (int64_t)(grow + srow) * h;
+    ctx->d2h_bytes += (int64_t)srow * h;
     CK(cudaMemcpy2DAsync(d_g, grow, guide->data, guide->step, grow, h, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpy2DAsync(d_s, srow, src->data, src->step, srow, h, cudaMemcpyHostToDevice, st));
     dwls_image G = *guide, Sm = *src, D = *dst;
@@ -1024,16 +1034,22 @@ extern "C" dwls_status dwls_fgs_weights_host(dwls_ctx* ctx, const dwls_image* gu
     return DWLS_OK;
 }
 
-// nf frames of `rows` rows of `row_bytes` between host and device: one transfer when both sides are dense, else one per
-// frame (dense rows) or a 2-D copy per frame.  dst_step < 0: the destination rows are dense (device staging).
+// nf frames of `rows` rows of `row_bytes` between host and device: one transfer when both sides are dense or when the rows
+// of all frames are equally spaced on both sides (a column window of a dense batch), else one per frame.
+// dst_step < 0: the destination rows are dense (device staging).
 static dwls_status copy_frames(dwls_ctx* ctx, void* dst, int64_t dst_frame, const void* src, int64_t src_frame, int64_t src_step,
                                size_t row_bytes, int rows, int nf, cudaMemcpyKind kind, cudaStream_t st, int64_t dst_step = -1)
 {
     if (dst_step < 0) dst_step = (int64_t)row_bytes;
+    (kind == cudaMemcpyHostToDevice ? ctx->h2d_bytes : ctx->d2h_bytes) += (int64_t)row_bytes * rows * nf;
     const bool dense_rows = src_step == (int64_t)row_bytes && dst_step == (int64_t)row_bytes;
     const int64_t frame_bytes = (int64_t)row_bytes * rows;
     if (dense_rows && (nf == 1 || (src_frame == frame_bytes && dst_frame == frame_bytes))) {
         CK(cudaMemcpyAsync(dst, src, (size_t)frame_bytes * nf, kind, st));
+        return DWLS_OK;
+    }
+    if (nf == 1 || (src_frame == src_step * rows && dst_frame == dst_step * rows)) {
+        CK(cudaMemcpy2DAsync(dst, (size_t)dst_step, src, (size_t)src_step, row_bytes, (size_t)rows * nf, kind, st));
         return DWLS_OK;
     }
     for (int f = 0; f < nf; ++f) {
@@ -1043,6 +1059,20 @@ static dwls_status copy_frames(dwls_ctx* ctx, void* dst, int64_t dst_frame, cons
         else CK(cudaMemcpy2DAsync(d, (size_t)dst_step, s, (size_t)src_step, row_bytes, rows, kind, st));
     }
     return DWLS_OK;
+}
+
+// the part of an input the kernels read: [lo - margin, lo + len + margin) clipped to [0, full), widened to multiples of
+// `align` elements.  The margin covers the bilinear taps of the half-resolution mode (disparity_filters.cpp:268-277);
+// staged cells outside the window keep whatever an earlier call left there and are never used.
+static void read_window(int lo, int len, int full, int margin, int align, int* w0, int* w1)
+{
+    int a = lo - margin, b = lo + len + margin;
+    if (a < 0) a = 0;
+    if (b > full) b = full;
+    a = a / align * align;
+    b = (b + align - 1) / align * align;
+    if (b > full) b = full;
+    *w0 = a; *w1 = b;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1087,10 +1117,20 @@ extern "C" dwls_status dwls_filter_batch_host(dwls_ctx* ctx, const dwls_batch* h
         uint8_t* d_dl = d; uint8_t* d_dr = d_dl + (size_t)G * f_dl; uint8_t* d_view = d_dr + (size_t)G * f_dl;
         uint8_t* d_out = d_view + (size_t)G * f_view; uint8_t* d_conf = d_out + (size_t)G * f_out;
         {
+            // upload only what the filter reads (the windows are whole frames when the ROI is the whole image)
             dwls_status cs;
-            if ((cs = copy_frames(ctx, d_dl, f_dl, (const uint8_t*)hb->disp_left + (size_t)f0 * hb->dl_frame, hb->dl_frame, hb->dl_step, (size_t)dw * 2, dh, nf, cudaMemcpyHostToDevice, st))) return cs;
-            if (useconf && (cs = copy_frames(ctx, d_dr, f_dl, (const uint8_t*)hb->disp_right + (size_t)f0 * hb->dr_frame, hb->dr_frame, hb->dr_step, (size_t)dw * 2, dh, nf, cudaMemcpyHostToDevice, st))) return cs;
-            if ((cs = copy_frames(ctx, d_view, f_view, hb->view + (size_t)f0 * hb->view_frame, hb->view_frame, hb->view_step, (size_t)W * vcn, H, nf, cudaMemcpyHostToDevice, st))) return cs;
+            int x0, x1, y0, y1;
+            read_window(g.ry, g.rh, dh, 8, 1, &y0, &y1);
+            if (y1 - y0 != dh) { y0 = 0; y1 = dh; }           // row windows would split the batch into one copy per frame: not worth it
+            read_window(g.rx, g.rw, dw, 8, 32, &x0, &x1);
+            if ((cs = copy_frames(ctx, d_dl + (size_t)x0 * 2, f_dl, (const uint8_t*)hb->disp_left + (size_t)f0 * hb->dl_frame + (size_t)x0 * 2, hb->dl_frame,
+                                  hb->dl_step, (size_t)(x1 - x0) * 2, dh, nf, cudaMemcpyHostToDevice, st, (int64_t)dw * 2))) return cs;
+            read_window(useconf ? g.rrx : 0, g.rw, dw, 8, 32, &x0, &x1);
+            if (useconf && (cs = copy_frames(ctx, d_dr + (size_t)x0 * 2, f_dl, (const uint8_t*)hb->disp_right + (size_t)f0 * hb->dr_frame + (size_t)x0 * 2,
+                                             hb->dr_frame, hb->dr_step, (size_t)(x1 - x0) * 2, dh, nf, cudaMemcpyHostToDevice, st, (int64_t)dw * 2))) return cs;
+            read_window(g.fx, g.fw, W, 8, 32, &x0, &x1);
+            if ((cs = copy_frames(ctx, d_view + (size_t)x0 * vcn, f_view, hb->view + (size_t)f0 * hb->view_frame + (size_t)x0 * vcn, hb->view_frame, hb->view_step,
+                                  (size_t)(x1 - x0) * vcn, H, nf, cudaMemcpyHostToDevice, st, (int64_t)W * vcn))) return cs;
         }
         dwls_batch b;
         memset(&b, 0, sizeof b);

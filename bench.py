@@ -251,19 +251,23 @@ def main():
         for _ in range(2):
             bf.filter_host(hl, hv, ho, hr, None, ROI)
         sync_all()
+        x0 = ctx.transfer_bytes()
         t0 = time.perf_counter()
         for _ in range(args.steps):
             bf.filter_host(hl, hv, ho, hr, None, ROI)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
+        x1 = ctx.transfer_bytes()
         assert torch.equal(ho.to(dev), out), "host-path result differs from the device-path result"
         if dist is not None:
             t = torch.tensor([dt], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
         e2e = {"value": world * B * args.steps * W * H / dt / 1e6, "unit": "Mpix/s",
-               "h2d_bytes_per_step": int(hv.numel() + 2 * hl.numel() + 2 * hr.numel()), "d2h_bytes_per_step": int(2 * ho.numel()),
-               "api": "dwls_filter_batch_host (pinned host buffers, 2-lane copy/compute pipeline)"}
+               "h2d_bytes_per_step": (x1[0] - x0[0]) // args.steps, "d2h_bytes_per_step": (x1[1] - x0[1]) // args.steps,
+               "host_input_bytes_per_step": int(hv.numel() + 2 * hl.numel() + 2 * hr.numel()),
+               "api": "dwls_filter_batch_host (pinned host buffers, 2-lane copy/compute pipeline; uploads the ROI windows the filter "
+                      "reads, bytes counted by the library from the copies it issues)"}
 
     if rank != 0:
         if dist is not None:

@@ -86,6 +86,10 @@ DWLS_API int         dwls_kernel_timing_report(dwls_ctx* ctx, const char** names
  * by dwls_kernel_launches include the replayed ones.  Timing mode always uses plain launches. */
 DWLS_API dwls_status dwls_set_cuda_graphs(dwls_ctx* ctx, int on);
 DWLS_API int64_t     dwls_graph_replays(const dwls_ctx* ctx);
+/* bytes the host-buffer entry points have moved over PCIe since the context was created (either pointer may be NULL).
+ * dwls_filter_batch_host uploads only the part of each input the filter reads: the ROI of the left disparity map and of
+ * the view, the mirrored ROI of the right disparity map (disparity_filters.cpp:202-203), each with a few pixels of margin. */
+DWLS_API void        dwls_transfer_bytes(const dwls_ctx* ctx, int64_t* h2d, int64_t* d2h);
 /* frames processed per kernel launch group in the batch entry point (0 = choose automatically) */
 DWLS_API dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames);
 
