@@ -25,6 +25,7 @@ struct dwls_ctx {
     int64_t launches = 0;
     int64_t h2d_bytes = 0, d2h_bytes = 0;                   // moved by the host-buffer entry points
     int group_frames = 0;
+    bool interleave = false;                                // confidence path: the two solver planes in one sector-interleaved array (SolveArgs::il)
     float* lut = nullptr; float lut_sigma = -1.f;           // per-sigma LUT cache (fgs_filter.cpp:150-154)
     void* ws = nullptr; size_t ws_bytes = 0;                // solver workspace (grow-only)
     void* stage = nullptr; size_t stage_bytes = 0;          // device staging of the host entry points
@@ -158,6 +159,13 @@ dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames)
     return DWLS_OK;
 }
 
+dwls_status dwls_set_plane_interleave(dwls_ctx* ctx, int on)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    ctx->interleave = on != 0;
+    return DWLS_OK;
+}
+
 dwls_status dwls_set_cuda_graphs(dwls_ctx* ctx, int on)
 {
     if (!ctx) return DWLS_BAD_ARG;
@@ -243,11 +251,11 @@ static bool plan_solver(int w, int h, SolvePlan* p)
     return true;
 }
 
-template <int S, int MAXT, int HM>
+template <int S, int MAXT, int HM, bool IL = false>
 static dwls_status launch_h_inst(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
     const size_t smem = hsolve_smem_bytes<S, HM>(pl.hK, a.pitch);
-    auto k = hsolve_kernel<S, MAXT, HM>;
+    auto k = hsolve_kernel<S, MAXT, HM, IL>;
     static int ctas_per_sm = 0, cached_K = 0; static size_t cached_smem = 0;
     if (smem > 227 * 1024) return fail(ctx, DWLS_UNSUPPORTED, "row too wide for the shared-memory stages of the row pass");
     if (!ctas_per_sm || cached_K != pl.hK || cached_smem != smem) {
@@ -268,6 +276,10 @@ static dwls_status launch_h_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
 template <int S>
 static dwls_status launch_h(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
+    if (a.il) {
+        if constexpr (S == 2) { if (pl.hM == 8) return launch_h_inst<2, 256, 8, true>(ctx, a, pl, frames, st); }
+        return fail(ctx, DWLS_CUDA_ERROR, "internal: interleaved planes need two planes and rows of at most 2048 pixels");
+    }
     if (pl.hM == 8) return launch_h_inst<S, 256, 8>(ctx, a, pl, frames, st);          // w <= 2048
     if (pl.hK <= 256) return launch_h_inst<S, 256, 16>(ctx, a, pl, frames, st);       // w <= 4096
     return launch_h_inst<S, 512, 16>(ctx, a, pl, frames, st);                         // w <= 8192: level 2 takes the generic loop
@@ -303,7 +315,7 @@ static dwls_status make_tmap(dwls_ctx* ctx, CUtensorMap* tm, const float* base, 
     return DWLS_OK;
 }
 
-template <int M, int S, int VC, int FIN, int MAXT, bool WB>
+template <int M, int S, int VC, int FIN, int MAXT, bool WB, bool IL = false>
 static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
     VTma g;
@@ -313,16 +325,19 @@ static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
     g.strips_total = g.strips_x * frames;
     const size_t smem = vsolve_smem_bytes<M, S, VC>(pl.vK, g.nb * g.rb, WB ? 2 : 1);
     if (smem > 227 * 1024) return fail(ctx, DWLS_UNSUPPORTED, "image too tall for the shared-memory stage of the column pass");
-    auto k = vsolve_kernel<M, S, VC, FIN, MAXT, WB>;
+    auto k = vsolve_kernel<M, S, VC, FIN, MAXT, WB, IL>;
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CUtensorMap tw, t0, t1;
     dwls_status s;
     const int64_t rows = (int64_t)frames * a.h;           // frames are contiguous planes: a.p_frame == a.w_frame == pitch * h
     if (WB) tw = CUtensorMap();
     else if ((s = make_tmap(ctx, &tw, a.weight, a.pitch, rows, VC, g.rb))) return s;
-    if ((s = make_tmap(ctx, &t0, a.in[0], a.pitch, rows, VC, g.rb))) return s;
-    if (S > 1) { if ((s = make_tmap(ctx, &t1, a.in[1], a.pitch, rows, VC, g.rb))) return s; }
-    else t1 = t0;
+    if (IL) { if ((s = make_tmap(ctx, &t0, a.in[0], S * a.pitch, rows, S * VC, g.rb))) return s; t1 = t0; }   // one box row = the strip of all planes
+    else {
+        if ((s = make_tmap(ctx, &t0, a.in[0], a.pitch, rows, VC, g.rb))) return s;
+        if (S > 1) { if ((s = make_tmap(ctx, &t1, a.in[1], a.pitch, rows, VC, g.rb))) return s; }
+        else t1 = t0;
+    }
     int per_sm = 1;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, VC * pl.vK, smem));
     if (per_sm < 1) return fail(ctx, DWLS_CUDA_ERROR, "column pass does not fit on an SM");
@@ -336,6 +351,10 @@ static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
 template <int S, int FIN>
 static dwls_status launch_v(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
+    if (a.il) {
+        if constexpr (S == 2) { if (pl.vM == 9 && pl.wstrip == 8) return launch_v_inst<9, 2, 8, FIN, 1024, true, true>(ctx, a, pl, frames, st); }
+        return fail(ctx, DWLS_CUDA_ERROR, "internal: interleaved planes need two planes and at most 1152 rows");
+    }
     if (pl.vM == 9) return pl.wstrip == 8 ? launch_v_inst<9, S, 8, FIN, 1024, true>(ctx, a, pl, frames, st)
                                           : launch_v_inst<9, S, 8, FIN, 1024, false>(ctx, a, pl, frames, st);
     // 1153..2176 rows, 17 rows per thread: a single plane still fits 8-column strips (32-byte rows) in 64 registers
@@ -610,6 +629,8 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
     int16_t* out = b->out ? (int16_t*)((uint8_t*)b->out + (size_t)f0 * b->out_frame) : nullptr;
     float* cexp = b->conf ? (float*)((uint8_t*)b->conf + (size_t)f0 * b->conf_frame) : nullptr;
 
+    // confidence path, rows of at most 2048 pixels and at most 1152 of them: the two planes share one interleaved array (p0 | p1)
+    const bool il = conf && !mask_only && ctx->interleave && g.plan.hM == 8 && g.plan.vM == 9 && !g.plan.vT && g.plan.wstrip == 8;
     bool out_border_done = false;
     if (conf) {
         dwls_status s2;
@@ -627,7 +648,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
         if (g.same) { a.conf = cexp; a.conf_step = b->conf_step / 4; a.conf_frame = b->conf_frame / 4; a.plane_dc = p0; a.plane_c = p1; }
         else { a.conf = conflo; a.conf_step = g.dw; a.conf_frame = L.conflo; a.plane_dc = nullptr; a.plane_c = nullptr; }
         if (mask_only) { a.conf = nullptr; a.plane_dc = nullptr; a.plane_c = nullptr; }
-        a.p_frame = L.plane; a.pitch = g.pitch;
+        a.p_frame = L.plane; a.pitch = g.pitch; a.il = il;
         a.mask = mask; a.mask_step = mask_step;
         if ((s2 = launch_conf(ctx, a, nf, st))) return s2;
         if (a.conf || a.mask) {          // zero the exported map (and the mask) outside the ROI (disparity_filters.cpp:187)
@@ -651,7 +672,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
         u.x_ratio = g.W / (float)g.dw;
         u.fx = g.fx; u.fy = g.fy; u.fw = g.fw; u.fh = g.fh;
         u.conf = conf ? cexp : nullptr; u.conf_step = b->conf_step / 4; u.conf_frame = b->conf_frame / 4;
-        u.plane_dc = p0; u.plane_c = conf ? p1 : nullptr; u.p_frame = L.plane; u.pitch = g.pitch;
+        u.plane_dc = p0; u.plane_c = conf ? p1 : nullptr; u.p_frame = L.plane; u.pitch = g.pitch; u.il = il;
         TIMED(K_UPSCALE, st, upscale_prep_kernel<<<dim3((upscale_groups(g.W, g.fx) + 127) / 128, g.H, nf), 128, 0, st>>>(u));
         CK(cudaGetLastError());
     } else if (!conf) {
@@ -674,7 +695,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
     SolveArgs a;
     memset(&a, 0, sizeof a);
     a.w_frame = L.plane; a.p_frame = L.plane; a.pitch = g.pitch; a.w = g.fw; a.h = g.fh;
-    a.in[0] = p0; a.out[0] = p0; a.in[1] = p1; a.out[1] = p1;
+    a.in[0] = p0; a.out[0] = p0; a.in[1] = p1; a.out[1] = p1; a.il = il;
     a.out16 = out + (size_t)g.fy * (b->out_step / 2) + g.fx; a.out16_step = b->out_step / 2; a.out16_frame = b->out_frame / 2;
     return run_sweeps(ctx, a, chor, cvert, conf ? 2 : 1, conf ? FIN_WLS : FIN_S16, g.plan, nf, p->lambda, p->lambda_attenuation, p->num_iter, st, &T);
 }
@@ -697,7 +718,7 @@ static dwls_status filter_frames_graphed(dwls_ctx* ctx, const dwls_batch* b, int
     const int no_roi[4] = { -1, -1, -1, -1 };
     put(roi_in ? roi_in : no_roi, sizeof no_roi);
     float* base = ws_base ? ws_base : (float*)ctx->ws;
-    PUT(base); PUT(ctx->lut);
+    PUT(base); PUT(ctx->lut); PUT(ctx->interleave);
 #undef PUT
     for (auto& ge : ctx->graph_cache)
         if (ge.key == key) {

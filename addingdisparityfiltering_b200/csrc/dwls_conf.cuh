@@ -26,8 +26,16 @@ struct ConfArgs {
     float* conf_r; int64_t cr_frame; int cr_pitch;    // right discontinuity map, ROI-cropped workspace, 0..1
     float* conf; int64_t conf_step, conf_frame;       // exported map (elements), full disparity size, 0..255; may be NULL
     float* plane_dc; float* plane_c; int64_t p_frame; int pitch;   // ROI-cropped solver planes; NULL in half-res mode
+    int il;                                           // planes interleaved sector by sector in ONE array at plane_dc (SolveArgs::il): d*c is plane 0, c plane 1
     uint8_t* mask; int64_t mask_step;                 // optional LRC decision export (frame 0 only)
 };
+
+// offset of (frame, row y, column c, plane s) in a solver plane pair, c = first column of an aligned run of <= 8 (SolveArgs::il)
+__device__ __forceinline__ size_t plane_off(int il, int64_t p_frame, int pitch, int frame, int y, int c, int s)
+{
+    return il ? (size_t)frame * (2 * p_frame) + (size_t)y * (2 * pitch) + (size_t)(c >> 3) * 16 + s * 8 + (c & 7)
+              : (size_t)frame * p_frame + (size_t)y * pitch + c;
+}
 
 __device__ __forceinline__ int reflect101(int p, int len)
 {
@@ -174,8 +182,8 @@ __global__ void __launch_bounds__(CF_T, 3) conf_kernel(const ConfArgs a)
 #pragma unroll
                     for (int i = 0; i < 8; ++i) if (i < nvalid) a.mask[(size_t)gy * a.mask_step + gx0 + i] = m[i];
                 if (a.plane_c) {
-                    float* PC = a.plane_c + (size_t)frame * a.p_frame + (size_t)y * a.pitch + cx0;
-                    float* PD = a.plane_dc + (size_t)frame * a.p_frame + (size_t)y * a.pitch + cx0;
+                    float* PC = (a.il ? a.plane_dc : a.plane_c) + plane_off(a.il, a.p_frame, a.pitch, frame, y, cx0, 1);
+                    float* PD = a.plane_dc + plane_off(a.il, a.p_frame, a.pitch, frame, y, cx0, 0);
                     if (nvalid == 8) {
                         *(float4*)PC = make_float4(cv[0], cv[1], cv[2], cv[3]); *((float4*)PC + 1) = make_float4(cv[4], cv[5], cv[6], cv[7]);
                         *(float4*)PD = make_float4(dc[0], dc[1], dc[2], dc[3]); *((float4*)PD + 1) = make_float4(dc[4], dc[5], dc[6], dc[7]);

@@ -23,6 +23,10 @@ struct SolveArgs {
     int pitch;               // floats between rows, multiple of 8, shared by all workspace planes
     int w, h;
     float lam;
+    // il != 0: the S = 2 planes live in ONE array (in[0] / out[0]) interleaved sector by sector, [row][col / 8][plane][8]:
+    // a row of both planes is one contiguous 2 * pitch floats (one bulk copy in the row pass) and an 8-column strip of both
+    // planes is 64 contiguous bytes per row (one TMA box row instead of two 32-byte ones in the column pass)
+    int il;
     // fused epilogue of the last column pass
     int16_t* out16;          // points at the ROI origin inside the full-size output
     int64_t out16_step;      // elements between rows
@@ -96,12 +100,15 @@ __host__ __device__ inline size_t hsolve_smem_bytes(int K, int pitch)
     return sizeof(float) * ((size_t)HST * (1 + S) * pitch + HL2BUF * (size_t)(4 + 2 * S) * l2pad_size(K) + 32 * (2 + S) * HM) + sizeof(uint64_t) * HST;
 }
 
-template <int S, int MAXT, int HM>
+template <int S, int MAXT, int HM, bool IL = false>
 __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : 2) : 1)) hsolve_kernel(const SolveArgs a, const int rows_total)
 {
     extern __shared__ __align__(128) float sm[];
     const int K = blockDim.x, M2 = K >> 5, KP = l2pad_size(K);
     const int t = threadIdx.x, j0 = t * HM;
+    // interleaved planes: threads whose bit 1 is set hold plane 1 in f[0] and plane 0 in f[1] (the planes are solved
+    // alike), which spreads a warp's 64-byte-strided reads over all banks instead of half of them
+    const int sel = IL ? ((t >> 1) & 1) : 0;
     float* stage0 = sm;                                           // [HST][1+S][pitch]
     float* l2base = sm + (size_t)HST * (1 + S) * a.pitch;         // [2][(4+2S)*KP]
     float* stash = l2base + HL2BUF * (4 + 2 * S) * KP;                 // [(2+S)*HM][32]: warp 0 parks its level-1 state here during level 2
@@ -109,15 +116,18 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : 2) : 1
     const uint32_t row_bytes = (uint32_t)a.pitch * 4u;
     const int n_mine = (rows_total - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
-    auto issue = [&](int i) {                                     // thread 0 only: fetch my i-th row into stage i % HST
-        const int gr = blockIdx.x + i * gridDim.x, frame = gr / a.h, row = gr - frame * a.h;
+    // my i-th row is number blockIdx.x + i * gridDim.x; its (frame, row in the frame) advance by a constant step
+    const int step_f = (int)gridDim.x / a.h, step_r = (int)gridDim.x - step_f * a.h;
+    auto issue = [&](int i, int frame, int row) {                 // thread 0 only: fetch my i-th row into stage i % HST
         float* dst = stage0 + (size_t)(i % HST) * (1 + S) * a.pitch;
         uint64_t* bar = full + (i % HST);
         mbar_arrive_expect_tx(bar, (1 + S) * row_bytes);
         bulk_g2s(dst, a.weight + (size_t)frame * a.w_frame + (size_t)row * a.pitch, row_bytes, bar);
+        if (IL) bulk_g2s(dst + a.pitch, a.in[0] + (size_t)frame * (S * a.p_frame) + (size_t)row * (S * a.pitch), S * row_bytes, bar);
+        else
 #pragma unroll
-        for (int s = 0; s < S; ++s)
-            bulk_g2s(dst + (size_t)(1 + s) * a.pitch, a.in[s] + (size_t)frame * a.p_frame + (size_t)row * a.pitch, row_bytes, bar);
+            for (int s = 0; s < S; ++s)
+                bulk_g2s(dst + (size_t)(1 + s) * a.pitch, a.in[s] + (size_t)frame * a.p_frame + (size_t)row * a.pitch, row_bytes, bar);
     };
 
     if (t == 0) {
@@ -125,11 +135,15 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : 2) : 1
         mbar_fence_init();
     }
     __syncthreads();
-    if (t == 0)
-        for (int i = 0; i < HST && i < n_mine; ++i) issue(i);
+    int frame = (int)blockIdx.x / a.h, row = (int)blockIdx.x - frame * a.h;
+    int pframe = frame, prow = row;                               // the row HST ahead (the one whose fetch is issued next)
+    for (int i = 0; i < HST; ++i) {
+        if (t == 0 && i < n_mine) issue(i, pframe, prow);
+        pframe += step_f; prow += step_r;
+        if (prow >= a.h) { prow -= a.h; ++pframe; }
+    }
 
     for (int i = 0; i < n_mine; ++i) {
-        const int gr = blockIdx.x + i * gridDim.x, frame = gr / a.h, row = gr - frame * a.h;
         const float* st = stage0 + (size_t)(i % HST) * (1 + S) * a.pitch;
         float* A = l2base + (size_t)(HL2BUF > 1 ? (i & 1) : 0) * (4 + 2 * S) * KP;
         float* B = A + KP; float* Bd = B + KP; float* C = Bd + KP; float* F = C + KP; float* Fd = F + S * KP;
@@ -146,7 +160,7 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : 2) : 1
             if (t > 0) aprev = a.lam * st[j0 - 1];
 #pragma unroll
             for (int s = 0; s < S; ++s) {
-                const float* P = st + (size_t)(1 + s) * a.pitch + j0;
+                const float* P = IL ? st + a.pitch + j0 * S + 8 * (s ^ sel) : st + (size_t)(1 + s) * a.pitch + j0;
 #pragma unroll
                 for (int q = 0; q < HM / 4; ++q) {
                     const float4 ff = *(const float4*)(P + 4 * q);
@@ -178,12 +192,12 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : 2) : 1
         const int p = l2pad(t);
         A[p] = o.A; B[p] = o.B;
 #pragma unroll
-        for (int s = 0; s < S; ++s) F[s * KP + p] = o.Fs[s];
+        for (int s = 0; s < S; ++s) F[(s ^ sel) * KP + p] = o.Fs[s];
         if (t > 0) {
             const int pm = l2pad(t - 1);
             C[pm] = o.Cn; Bd[pm] = o.dB;
 #pragma unroll
-            for (int s = 0; s < S; ++s) Fd[s * KP + pm] = o.dF[s];
+            for (int s = 0; s < S; ++s) Fd[(s ^ sel) * KP + pm] = o.dF[s];
         }
         if (t == K - 1) {
             C[p] = 0.f; Bd[p] = 0.f;
@@ -191,7 +205,9 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : 2) : 1
             for (int s = 0; s < S; ++s) Fd[s * KP + p] = 0.f;
         }
         __syncthreads();                       // level-2 rows complete; every thread is done reading this stage
-        if (t == 0 && i + HST < n_mine) issue(i + HST);
+        if (t == 0 && i + HST < n_mine) issue(i + HST, pframe, prow);
+        pframe += step_f; prow += step_r;
+        if (prow >= a.h) { prow -= a.h; ++pframe; }
         if (t < 32) {
             // the level-2 warp needs its registers for the reduced system: park the level-1 state in shared memory meanwhile
 #pragma unroll
@@ -211,18 +227,21 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : 2) : 1
         __syncthreads();
         float Uown[S], Uprev[S];
 #pragma unroll
-        for (int s = 0; s < S; ++s) { Uown[s] = F[s * KP + p]; Uprev[s] = (t > 0) ? F[s * KP + l2pad(t - 1)] : 0.f; }
+        for (int s = 0; s < S; ++s) { Uown[s] = F[(s ^ sel) * KP + p]; Uprev[s] = (t > 0) ? F[(s ^ sel) * KP + l2pad(t - 1)] : 0.f; }
         if (HL2BUF == 1) __syncthreads();       // the single scratch copy is rewritten by the next row
         level1_fixup<HM, S>(c, f, v, Uprev, Uown);
         if (j0 < a.w) {
 #pragma unroll
             for (int s = 0; s < S; ++s) {
-                float* P = a.out[s] + (size_t)frame * a.p_frame + (size_t)row * a.pitch + j0;
+                float* P = IL ? a.out[0] + (size_t)frame * (S * a.p_frame) + (size_t)row * (S * a.pitch) + j0 * S + 8 * (s ^ sel)
+                              : a.out[s] + (size_t)frame * a.p_frame + (size_t)row * a.pitch + j0;
 #pragma unroll
                 for (int q = 0; q < HM / 8; ++q)                  // full 32-byte sectors, one 256-bit store each
                     if (q == 0 || j0 + 8 * q < a.pitch) st_global_v8(P + 8 * q, f[s][8 * q], f[s][8 * q + 1], f[s][8 * q + 2], f[s][8 * q + 3], f[s][8 * q + 4], f[s][8 * q + 5], f[s][8 * q + 6], f[s][8 * q + 7]);
             }
         }
+        frame += step_f; row += step_r;
+        if (row >= a.h) { row -= a.h; ++frame; }
     }
 }
 
@@ -256,7 +275,7 @@ __host__ __device__ inline size_t vsolve_smem_bytes(int K, int rows_staged, int 
 // copy into one of two buffers, requested a whole strip ahead (the weights are only read by level 1, so their buffer is
 // free again long before the data planes' stage is); otherwise it is row-major like the data planes and arrives as TMA
 // boxes together with them.
-template <int M, int S, int VC, int FIN, int MAXT, bool WB>
+template <int M, int S, int VC, int FIN, int MAXT, bool WB, bool IL = false>
 __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const VTma g, const __grid_constant__ CUtensorMap tm_w,
                                                       const __grid_constant__ CUtensorMap tm_p0, const __grid_constant__ CUtensorMap tm_p1)
 {
@@ -272,23 +291,28 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
     uint64_t* full = (uint64_t*)(stash + (size_t)VC * 32 * (2 + S) * M);
     uint64_t* wfull = full + 1;                                   // [2]
     const int t = threadIdx.x, x = t % VC, k = t / VC, r0 = k * M;
+    // interleaved planes: every other pair of chunks holds plane 1 in f[0] and plane 0 in f[1], so that the four chunks of a
+    // warp read four different bank groups of the [row][plane][VC] stage
+    const int sel = IL ? ((k >> 1) & 1) : 0;
     float* A = l2base + x * SYS; float* B = A + KP; float* Bd = B + KP; float* C = Bd + KP;
     float* F = C + KP; float* Fd = F + S * KP;
     const int n_mine = (g.strips_total - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     const uint32_t tx_bytes = (uint32_t)(((WB ? 0 : rows_staged) + S * rows_staged) * VC * sizeof(float));
 
-    auto issue = [&](int i) {                                     // thread 0: fetch the data planes of my i-th strip
-        const int si = blockIdx.x + i * gridDim.x, frame = si / g.strips_x, col0 = (si - frame * g.strips_x) * VC;
+    // my i-th strip is number blockIdx.x + i * gridDim.x; its (frame, strip in the frame) advance by a constant step
+    const int step_f = (int)gridDim.x / g.strips_x, step_s = (int)gridDim.x - step_f * g.strips_x;
+    auto issue = [&](int frame, int strip) {                      // thread 0: fetch the data planes of a strip
+        const int col0 = strip * VC;
         mbar_arrive_expect_tx(full, tx_bytes);
         for (int b = 0; b < g.nb; ++b) {
             const int grow = frame * a.h + b * g.rb;
             if (!WB) tma_load_2d(wstage + (size_t)b * g.rb * VC, &tm_w, col0, grow, full);
+            if (IL) { tma_load_2d(stage + (size_t)(b * g.rb) * (VC * S), &tm_p0, col0 * S, grow, full); continue; }   // [row][plane][VC]
             tma_load_2d(stage + (size_t)(b * g.rb) * VC, &tm_p0, col0, grow, full);
             if (S > 1) tma_load_2d(stage + (size_t)(rows_staged + b * g.rb) * VC, &tm_p1, col0, grow, full);
         }
     };
-    auto issue_w = [&](int i) {                                   // thread 0: fetch the weight strip of my i-th strip
-        const int si = blockIdx.x + i * gridDim.x, frame = si / g.strips_x, strip = si - frame * g.strips_x;
+    auto issue_w = [&](int i, int frame, int strip) {             // thread 0: fetch the weight strip of my i-th strip
         const uint32_t bytes = (uint32_t)(a.h * VC * sizeof(float));
         mbar_arrive_expect_tx(wfull + (i & 1), bytes);
         bulk_g2s(wstage + (size_t)(i & 1) * rows_staged * VC, a.weight + (size_t)frame * a.w_frame + (size_t)strip * ((size_t)a.h * VC), bytes, wfull + (i & 1));
@@ -296,13 +320,16 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
 
     if (t == 0) { mbar_init(full, 1); mbar_init(wfull, 1); mbar_init(wfull + 1, 1); mbar_fence_init(); }
     __syncthreads();
-    if (t == 0 && n_mine > 0) { if (WB) issue_w(0); issue(0); }
+    int frame = (int)blockIdx.x / g.strips_x, strip = (int)blockIdx.x - frame * g.strips_x;
+    if (t == 0 && n_mine > 0) { if (WB) issue_w(0, frame, strip); issue(frame, strip); }
 
     for (int i = 0; i < n_mine; ++i) {
-        const int si = blockIdx.x + i * gridDim.x, frame = si / g.strips_x, col = (si - frame * g.strips_x) * VC + x;
+        const int col = strip * VC + x;
         const bool live = col < a.w;
+        int nframe = frame + step_f, nstrip = strip + step_s;    // my next strip
+        if (nstrip >= g.strips_x) { nstrip -= g.strips_x; ++nframe; }
         if (WB) {
-            if (t == 0 && i + 1 < n_mine) issue_w(i + 1);        // its buffer was last read by level 1 of strip i-1
+            if (t == 0 && i + 1 < n_mine) issue_w(i + 1, nframe, nstrip);   // its buffer was last read by level 1 of strip i-1
             mbar_wait(wfull + (i & 1), (uint32_t)((i >> 1) & 1));
         }
         mbar_wait(full, (uint32_t)(i & 1));
@@ -310,13 +337,15 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
         float aprev = 0.f;
         {
             const float* sw = wstage + (size_t)(WB ? (i & 1) : 0) * rows_staged * VC + (size_t)r0 * VC + x;
-            const float* sp = stage + (size_t)r0 * VC + x;
+            const float* sp = stage + (size_t)r0 * (IL ? VC * S : VC) + x;
+            constexpr int SPM = IL ? VC * S : VC;                        // floats between rows of a staged plane
+            const int sps = IL ? VC : rows_staged * VC;                  // floats between planes
             if (live && r0 + M < a.h) {                                  // chunk strictly inside the column: no masks
 #pragma unroll
                 for (int m = 0; m < M; ++m) {
                     c[m] = a.lam * sw[m * VC];
 #pragma unroll
-                    for (int s = 0; s < S; ++s) f[s][m] = sp[(size_t)s * rows_staged * VC + m * VC];
+                    for (int s = 0; s < S; ++s) f[s][m] = sp[(s ^ sel) * sps + m * SPM];
                 }
             } else {
 #pragma unroll
@@ -324,7 +353,7 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
                     const bool in = live && (r0 + m < a.h);
                     c[m] = (live && (r0 + m < a.h - 1)) ? a.lam * sw[m * VC] : 0.f;              // last row weight 0 (fgs_filter.cpp:658-660)
 #pragma unroll
-                    for (int s = 0; s < S; ++s) f[s][m] = in ? sp[(size_t)s * rows_staged * VC + m * VC] : 0.f;
+                    for (int s = 0; s < S; ++s) f[s][m] = in ? sp[(s ^ sel) * sps + m * SPM] : 0.f;
                 }
             }
             if (live && k > 0 && r0 - 1 < a.h - 1) aprev = a.lam * sw[-VC];
@@ -333,12 +362,12 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
         const int p = l2pad(k);
         A[p] = o.A; B[p] = o.B;
 #pragma unroll
-        for (int s = 0; s < S; ++s) F[s * KP + p] = o.Fs[s];
+        for (int s = 0; s < S; ++s) F[(s ^ sel) * KP + p] = o.Fs[s];
         if (k > 0) {
             const int pm = l2pad(k - 1);
             C[pm] = o.Cn; Bd[pm] = o.dB;
 #pragma unroll
-            for (int s = 0; s < S; ++s) Fd[s * KP + pm] = o.dF[s];
+            for (int s = 0; s < S; ++s) Fd[(s ^ sel) * KP + pm] = o.dF[s];
         }
         if (k == K - 1) {
             C[p] = 0.f; Bd[p] = 0.f;
@@ -346,7 +375,7 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
             for (int s = 0; s < S; ++s) Fd[s * KP + p] = 0.f;
         }
         __syncthreads();                       // level-2 rows complete; the stage has been read by everyone
-        if (t == 0 && i + 1 < n_mine) issue(i + 1);
+        if (t == 0 && i + 1 < n_mine) issue(nframe, nstrip);
         {
             const int warp = t >> 5, nwarps = blockDim.x >> 5, lane = t & 31;
             if (warp < VC) {
@@ -373,26 +402,32 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
         __syncthreads();
         float Uown[S], Uprev[S];
 #pragma unroll
-        for (int s = 0; s < S; ++s) { Uown[s] = F[s * KP + p]; Uprev[s] = (k > 0) ? F[s * KP + l2pad(k - 1)] : 0.f; }
+        for (int s = 0; s < S; ++s) { Uown[s] = F[(s ^ sel) * KP + p]; Uprev[s] = (k > 0) ? F[(s ^ sel) * KP + l2pad(k - 1)] : 0.f; }
         __syncthreads();                       // level-2 scratch may be overwritten by the next strip from here on
         level1_fixup<M, S>(c, f, v, Uprev, Uown);
         if (live) {
-            const size_t off0 = (size_t)frame * a.p_frame + (size_t)r0 * a.pitch + col;
+            const size_t off0 = IL ? (size_t)frame * (S * a.p_frame) + (size_t)r0 * (S * a.pitch) + (size_t)(col - x) * S + x
+                                   : (size_t)frame * a.p_frame + (size_t)r0 * a.pitch + col;
+            const int opitch = IL ? S * a.pitch : a.pitch;
             const int nrow = min(M, a.h - r0);                           // rows of this chunk inside the image (<= 0 for padding chunks)
             if (FIN == FIN_FLOAT) {
 #pragma unroll
                 for (int s = 0; s < S; ++s) {
-                    float* O = a.out[s] + off0;
+                    float* O = IL ? a.out[0] + off0 + (s ^ sel) * VC : a.out[s] + off0;
                     if (nrow == M) {
 #pragma unroll
-                        for (int m = 0; m < M; ++m) O[m * a.pitch] = f[s][m];
+                        for (int m = 0; m < M; ++m) O[m * opitch] = f[s][m];
                     } else {
 #pragma unroll
-                        for (int m = 0; m < M; ++m) if (m < nrow) O[m * a.pitch] = f[s][m];
+                        for (int m = 0; m < M; ++m) if (m < nrow) O[m * opitch] = f[s][m];
                     }
                 }
             } else {
                 int16_t* O = a.out16 + (size_t)frame * a.out16_frame + (size_t)r0 * a.out16_step + col;
+                if (IL && sel) {                                         // this chunk holds the planes the other way round
+#pragma unroll
+                    for (int m = 0; m < M; ++m) { const float q = f[0][m]; f[0][m] = f[S - 1][m]; f[S - 1][m] = q; }
+                }
                 if (nrow == M) {
 #pragma unroll
                     for (int m = 0; m < M; ++m) O[(size_t)m * a.out16_step] = cvt_s16((FIN == FIN_WLS) ? wls_normalise(f[0][m], f[S - 1][m]) : f[0][m]);
@@ -403,6 +438,7 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
                 }
             }
         }
+        frame = nframe; strip = nstrip;
     }
 }
 

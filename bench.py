@@ -162,6 +162,7 @@ def main():
     ap.add_argument("--group", type=int, default=0, help="frames per kernel launch group (0 = library default)")
     ap.add_argument("--ref-frames", type=int, default=4)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--interleave", action="store_true", help="A/B switch: sector-interleaved solver planes (dwls_set_plane_interleave)")
     ap.add_argument("--gather", action="store_true", help="all_gather the outputs over NCCL inside the timed region")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (tuning runs only)")
@@ -184,6 +185,8 @@ def main():
     ctx = A.Context(local)
     if args.group:
         ctx.set_group_frames(args.group)
+    if args.interleave:
+        ctx.set_plane_interleave(True)
     B = args.frames
 
     base = make_base_frames(2)

@@ -309,3 +309,30 @@ def test_wls_zero_confidence_everywhere(ctx):
     assert hit.any()
     assert (f.getConfidenceMap() == ref["conf"]).all()
     assert (got == ref["out"]).all(), (np.unique(got), np.unique(ref["out"]))
+
+
+@pytest.mark.parametrize("case", ["full", "half", "odd_rows", "narrow", "radius9"])
+def test_plane_layouts_give_identical_results(ctx, case):
+    """The two solver planes of the confidence path travel between the sweeps either as two row-major planes or as one
+    sector-interleaved array (dwls_set_plane_interleave): same arithmetic per thread, so the outputs must be bit-identical,
+    and both are checked against the oracle."""
+    import cv2
+    w, h, radius = {"full": (640, 480, 2), "half": (640, 480, 3), "odd_rows": (328, 123, 5), "narrow": (45, 31, 1), "radius9": (320, 96, 9)}[case]
+    view, dl, dr, roi = synth.make_artificial_example(w, h, 3, seed=11 * w + h)
+    if case == "half":
+        dl = (cv2.resize(dl, None, fx=0.5, fy=0.5) // 2).astype(np.int16)
+        dr = (cv2.resize(dr, None, fx=0.5, fy=0.5) // 2).astype(np.int16)
+        roi = (roi[0] // 2, roi[1] // 2, roi[2] // 2, roi[3] // 2)
+    outs, confs = [], []
+    try:
+        for on in (False, True):
+            ctx.set_plane_interleave(on)
+            _check_wls(ctx, view, dl, dr, roi, True, radius=radius)
+            f = A.createDisparityWLSFilterGeneric(True, ctx=ctx)
+            f.setSigmaColor(1.5); f.setDepthDiscontinuityRadius(radius)
+            outs.append(f.filter(dl, view, None, dr, roi).copy())
+            confs.append(f.getConfidenceMap().copy())
+    finally:
+        ctx.set_plane_interleave(True)
+    assert (outs[0] == outs[1]).all()
+    assert (confs[0] == confs[1]).all()
