@@ -56,20 +56,25 @@ __device__ __forceinline__ uint8_t cvt_u8(float v)
 }
 // disparity_filters.cpp:295: d*c~ .mul( 1 / (c~ + EPS) ), EPS = 1e-43f (denormal, line 47)
 __device__ __forceinline__ float wls_den(float c) { return __fadd_rn(fmaxf(c, 0.0f), __int_as_float(71)); }   // 71 * 2^-149 == 1e-43f
-// den and 1/den both normal numbers (2^-126 <= den < 2^125): one unsigned compare on the bit pattern (den >= 0)
-__device__ __forceinline__ bool wls_den_normal(float den) { return (uint32_t)(__float_as_int(den) - 0x00800000) < (uint32_t)(0x7e000000 - 0x00800000); }
-// MUFU.RCP and one Newton step: the correctly rounded reciprocal (up to ties 2^-22 apart), which is what the
-// reference's IEEE division returns; only valid when wls_den_normal(den)
-__device__ __forceinline__ float wls_rcp_fast(float den)
+// fl(1 / den) for 0 < den < 2^64, subnormal den included, without a branch: a tiny den is first scaled by 2^64 (exact), the
+// reciprocal taken as MUFU.RCP + one Newton step (the correctly rounded reciprocal up to ties 2^-22 apart, which is what
+// the reference's IEEE division returns) and scaled back (exact, or overflow to +inf exactly where 1 / den overflows).
+// Zero confidence next to sharp guide edges leaves the filtered confidence at 0 or subnormal over whole regions, so this
+// range is common, not an edge case.
+__device__ __forceinline__ float wls_rcp_scaled(float den)
 {
+    const float sc = den < 8.6736174e-19f ? 18446744073709551616.0f : 1.0f;       // 2^-60 : 2^64
+    const float ds = __fmul_rn(den, sc);
     float r;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(den));
-    return fmaf(r, fmaf(-den, r, 1.0f), r);
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(ds));
+    r = fmaf(r, fmaf(-ds, r, 1.0f), r);
+    return __fmul_rn(r, sc);
 }
+__device__ __forceinline__ bool wls_den_huge(float den) { return !(den < 18446744073709551616.0f); }   // never with confidences <= 255 (NaN counts as huge)
 __device__ __forceinline__ float wls_normalise(float dc, float c)
 {
     const float den = wls_den(c);
-    return __fmul_rn(dc, wls_den_normal(den) ? wls_rcp_fast(den) : __fdiv_rn(1.0f, den));
+    return __fmul_rn(dc, wls_den_huge(den) ? __fdiv_rn(1.0f, den) : wls_rcp_scaled(den));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -428,13 +433,27 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
 #pragma unroll
                     for (int m = 0; m < M; ++m) { const float q = f[0][m]; f[0][m] = f[S - 1][m]; f[S - 1][m] = q; }
                 }
+                if (FIN == FIN_WLS) {
+                    // one range test for the chunk, then straight-line code (the exact division is for denominators no
+                    // confidence map produces)
+                    bool huge = false;
+#pragma unroll
+                    for (int m = 0; m < M; ++m) { f[S - 1][m] = wls_den(f[S - 1][m]); huge |= wls_den_huge(f[S - 1][m]); }
+                    if (!huge) {
+#pragma unroll
+                        for (int m = 0; m < M; ++m) f[0][m] = __fmul_rn(f[0][m], wls_rcp_scaled(f[S - 1][m]));
+                    } else {
+#pragma unroll
+                        for (int m = 0; m < M; ++m) f[0][m] = __fmul_rn(f[0][m], __fdiv_rn(1.0f, f[S - 1][m]));
+                    }
+                }
                 if (nrow == M) {
 #pragma unroll
-                    for (int m = 0; m < M; ++m) O[(size_t)m * a.out16_step] = cvt_s16((FIN == FIN_WLS) ? wls_normalise(f[0][m], f[S - 1][m]) : f[0][m]);
+                    for (int m = 0; m < M; ++m) O[(size_t)m * a.out16_step] = cvt_s16(f[0][m]);
                 } else {
 #pragma unroll
                     for (int m = 0; m < M; ++m)
-                        if (m < nrow) O[(size_t)m * a.out16_step] = cvt_s16((FIN == FIN_WLS) ? wls_normalise(f[0][m], f[S - 1][m]) : f[0][m]);
+                        if (m < nrow) O[(size_t)m * a.out16_step] = cvt_s16(f[0][m]);
                 }
             }
         }

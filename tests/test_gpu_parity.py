@@ -336,3 +336,20 @@ def test_plane_layouts_give_identical_results(ctx, case):
         ctx.set_plane_interleave(True)
     assert (outs[0] == outs[1]).all()
     assert (confs[0] == confs[1]).all()
+
+
+def test_wls_zero_confidence_regions_next_to_sharp_edges(ctx):
+    """Half of the ROI fails the LRC check under a noisy guide (weights ~ 0), so the filtered confidence stays 0 or
+    subnormal over whole regions: 1 / (c~ + 1e-43f) overflows there and the reference writes -32768
+    (disparity_filters.cpp:295-296).  The final kernel takes that range without a branch (scaled reciprocal)."""
+    rng = np.random.default_rng(3)
+    w, h = 640, 480
+    view = rng.integers(0, 256, (h, w, 3)).astype(np.uint8)
+    dl = (np.full((h, w), 160) + rng.integers(-3, 4, (h, w))).astype(np.int16)
+    dr = (-dl).astype(np.int16)
+    dr[:, : w // 2] = 5000
+    roi = (32, 0, w - 32, h)
+    st = _check_wls(ctx, view, dl, dr, roi, True, radius=2)
+    ref = O.wls_filter(dl, view, dr, roi=roi, lam=8000.0, sigma=1.5, disc_radius=2)
+    assert (ref["out"][:, 32:] == -32768).mean() > 0.3          # the case really exercises the overflow range
+    print("zero-confidence regions parity", st)
