@@ -10,6 +10,8 @@
 #include <functional>
 #include <string>
 #include <vector>
+#include <unordered_map>
+#include <unordered_set>
 
 #include "../../include/dwls_b200.h"
 #include "dwls_resize.cuh"
@@ -44,6 +46,10 @@ struct dwls_ctx {
     std::vector<size_t> seen_once;
     uint64_t graph_clock = 0;
     int64_t graph_replays = 0;
+    // per-context (= per-device) kernel set-up: function attributes are per device, and contexts may live on different threads
+    struct HCache { int ctas_per_sm = 0, K = 0; size_t smem = 0; };
+    std::unordered_map<const void*, HCache> hcache;          // row-pass occupancy, by kernel instance
+    std::unordered_set<const void*> smem_attr_done;          // kernels whose dynamic shared-memory limit has been raised
 };
 
 enum KernelId { K_LUT = 0, K_WEIGHTS, K_CONF_R, K_CONF_L, K_UPSCALE, K_PREP, K_FILL, K_HSOLVE, K_VSOLVE, K_VSOLVE_FIN, K_UNPACK, K_PACK, K_TRANSPOSE, K_COUNT };
@@ -256,16 +262,17 @@ static dwls_status launch_h_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
 {
     const size_t smem = hsolve_smem_bytes<S, HM>(pl.hK, a.pitch);
     auto k = hsolve_kernel<S, MAXT, HM, IL>;
-    static int ctas_per_sm = 0, cached_K = 0; static size_t cached_smem = 0;
     if (smem > 227 * 1024) return fail(ctx, DWLS_UNSUPPORTED, "row too wide for the shared-memory stages of the row pass");
-    if (!ctas_per_sm || cached_K != pl.hK || cached_smem != smem) {
+    dwls_ctx::HCache& hc = ctx->hcache[(const void*)k];
+    if (!hc.ctas_per_sm || hc.K != pl.hK || hc.smem != smem) {
+        int per_sm = 0;
         CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k, pl.hK, smem));
-        if (ctas_per_sm < 1) return fail(ctx, DWLS_CUDA_ERROR, "row pass does not fit on an SM");
-        cached_K = pl.hK; cached_smem = smem;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, pl.hK, smem));
+        if (per_sm < 1) return fail(ctx, DWLS_CUDA_ERROR, "row pass does not fit on an SM");
+        hc.ctas_per_sm = per_sm; hc.K = pl.hK; hc.smem = smem;
     }
     const int rows_total = a.h * frames;
-    int grid = ctx->num_sms * ctas_per_sm;
+    int grid = ctx->num_sms * hc.ctas_per_sm;
     if (grid > rows_total) grid = rows_total;
     KTimer kt_(ctx, K_HSOLVE, st);
     k<<<grid, pl.hK, smem, st>>>(a, rows_total);
@@ -494,21 +501,21 @@ static bool make_tmap_s16(dwls_ctx* ctx, CUtensorMap* tm, const int16_t* base, i
 
 // confidence stage: right view first (its map is gathered by the left view's LRC step)
 template <int R, bool LEFT, bool TMA>
-static void launch_conf_inst(const ConfArgs& a, int G, dim3 grid, cudaStream_t st, const CUtensorMap& tm)
+static void launch_conf_inst(dwls_ctx* ctx, const ConfArgs& a, int G, dim3 grid, cudaStream_t st, const CUtensorMap& tm)
 {
     const size_t smem = conf_run_smem(R, LEFT);
-    static bool attr_set = false;
-    if (!attr_set) { cudaFuncSetAttribute(conf_run_kernel<R, LEFT, TMA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr_set = true; }
-    conf_run_kernel<R, LEFT, TMA><<<grid, CR_T, smem, st>>>(a, G, tm);
+    auto k = conf_run_kernel<R, LEFT, TMA>;
+    if (ctx->smem_attr_done.insert((const void*)k).second) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k<<<grid, CR_T, smem, st>>>(a, G, tm);
 }
 
 template <int R>
-static void launch_conf_run(const ConfArgs& a, int G, dim3 grid, cudaStream_t st, bool left, const CUtensorMap* tm)
+static void launch_conf_run(dwls_ctx* ctx, const ConfArgs& a, int G, dim3 grid, cudaStream_t st, bool left, const CUtensorMap* tm)
 {
     CUtensorMap none;
     memset(&none, 0, sizeof none);
-    if (left) { if (tm) launch_conf_inst<R, true, true>(a, G, grid, st, *tm); else launch_conf_inst<R, true, false>(a, G, grid, st, none); }
-    else { if (tm) launch_conf_inst<R, false, true>(a, G, grid, st, *tm); else launch_conf_inst<R, false, false>(a, G, grid, st, none); }
+    if (left) { if (tm) launch_conf_inst<R, true, true>(ctx, a, G, grid, st, *tm); else launch_conf_inst<R, true, false>(ctx, a, G, grid, st, none); }
+    else { if (tm) launch_conf_inst<R, false, true>(ctx, a, G, grid, st, *tm); else launch_conf_inst<R, false, false>(ctx, a, G, grid, st, none); }
 }
 
 static dwls_status launch_conf(dwls_ctx* ctx, const ConfArgs& a, int frames, cudaStream_t st)
@@ -525,14 +532,14 @@ static dwls_status launch_conf(dwls_ctx* ctx, const ConfArgs& a, int frames, cud
             const CUtensorMap* ptm = tma ? &tm : nullptr;
             KTimer kt_(ctx, left ? K_CONF_L : K_CONF_R, st);
             switch (a.radius) {
-            case 0: launch_conf_run<0>(a, G, grid, st, left, ptm); break;
-            case 1: launch_conf_run<1>(a, G, grid, st, left, ptm); break;
-            case 2: launch_conf_run<2>(a, G, grid, st, left, ptm); break;
-            case 3: launch_conf_run<3>(a, G, grid, st, left, ptm); break;
-            case 4: launch_conf_run<4>(a, G, grid, st, left, ptm); break;
-            case 5: launch_conf_run<5>(a, G, grid, st, left, ptm); break;
-            case 6: launch_conf_run<6>(a, G, grid, st, left, ptm); break;
-            default: launch_conf_run<7>(a, G, grid, st, left, ptm); break;
+            case 0: launch_conf_run<0>(ctx, a, G, grid, st, left, ptm); break;
+            case 1: launch_conf_run<1>(ctx, a, G, grid, st, left, ptm); break;
+            case 2: launch_conf_run<2>(ctx, a, G, grid, st, left, ptm); break;
+            case 3: launch_conf_run<3>(ctx, a, G, grid, st, left, ptm); break;
+            case 4: launch_conf_run<4>(ctx, a, G, grid, st, left, ptm); break;
+            case 5: launch_conf_run<5>(ctx, a, G, grid, st, left, ptm); break;
+            case 6: launch_conf_run<6>(ctx, a, G, grid, st, left, ptm); break;
+            default: launch_conf_run<7>(ctx, a, G, grid, st, left, ptm); break;
             }
             CK(cudaGetLastError());
         }

@@ -410,7 +410,30 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
         for (int s = 0; s < S; ++s) { Uown[s] = F[(s ^ sel) * KP + p]; Uprev[s] = (k > 0) ? F[(s ^ sel) * KP + l2pad(k - 1)] : 0.f; }
         __syncthreads();                       // level-2 scratch may be overwritten by the next strip from here on
         level1_fixup<M, S>(c, f, v, Uprev, Uown);
-        if (live) {
+        constexpr bool PAIR = (FIN == FIN_FLOAT && S == 2 && !IL && VC % 2 == 0 && M % 2 == 1);
+        if (PAIR) {
+            // neighbouring columns swap every other row, so that a lane stores TWO adjacent columns of one row with a 64-bit
+            // store: even columns keep rows 0, 2, .., odd columns rows 1, 3, ..; the last row (M - 1) pairs plane 0 (even
+            // columns) with plane 1 (odd columns).  Half as many store instructions for the LSU queue (9 instead of 18).
+            const bool odd = x & 1;
+            const int nrow = min(M, a.h - r0);
+            float* Ob = a.out[0] + (size_t)frame * a.p_frame + (size_t)r0 * a.pitch + (col - (x & 1));
+            const size_t dplane = (size_t)(a.out[1] - a.out[0]);
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+#pragma unroll
+                for (int m = 0; m + 1 < M; m += 2) {
+                    const float got = __shfl_xor_sync(0xffffffffu, odd ? f[s][m] : f[s][m + 1], 1);
+                    const float lo = odd ? got : f[s][m], hi = odd ? f[s][m + 1] : got;
+                    const int mr = m + (odd ? 1 : 0);
+                    if (mr < nrow) *(float2*)(Ob + s * dplane + (size_t)mr * a.pitch) = make_float2(lo, hi);
+                }
+            }
+            const float got = __shfl_xor_sync(0xffffffffu, odd ? f[0][M - 1] : f[1][M - 1], 1);
+            const float lo = odd ? got : f[0][M - 1], hi = odd ? f[1][M - 1] : got;
+            if (M - 1 < nrow) *(float2*)(Ob + (odd ? dplane : 0) + (size_t)(M - 1) * a.pitch) = make_float2(lo, hi);
+        }
+        if (live && !PAIR) {
             const size_t off0 = IL ? (size_t)frame * (S * a.p_frame) + (size_t)r0 * (S * a.pitch) + (size_t)(col - x) * S + x
                                    : (size_t)frame * a.p_frame + (size_t)r0 * a.pitch + col;
             const int opitch = IL ? S * a.pitch : a.pitch;
