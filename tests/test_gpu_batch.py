@@ -150,3 +150,42 @@ def test_graph_replay_matches_plain_launches():
     outs = [f.filter(frames[0][1], frames[0][0], None, frames[0][2], roi).copy() for _ in range(4)]
     assert all((o == outs[0]).all() for o in outs)
     assert (outs[0] == ref_out[0].cpu().numpy()).all()
+
+
+def test_config5_batch_of_512_frames_1080p(ctx):
+    """BASELINE.json configs[4] at full size: 512 independent 1080p stereo pairs in one device-resident batch call
+    (16 launch groups of 32 frames).  The oracle needs ~75 ms per frame, so the full batch is checked through
+    size-independent properties: every frame is one of four distinct stereo pairs, so (a) copies of a pair must come out
+    bit-identical wherever they sit in the batch and in its launch groups, (b) the four distinct results must equal
+    single-frame filter() calls bit for bit (frames are independent, disparity_filters.cpp:138-139), one of which is
+    checked against the oracle, and (c) everything outside the ROI is the -16 fill / zero confidence."""
+    import torch
+    W, H, B, NB = 1920, 1080, 512, 4
+    roi = (160, 0, 1760, 1080)
+    dev = torch.device("cuda", 0)
+    base = [synth.make_textured_scene(W, H, 3, seed=900 + i, max_disp=160) for i in range(NB)]
+    order = np.random.default_rng(5).integers(0, NB, B)
+    order[:NB] = np.arange(NB)
+    idx = torch.from_numpy(order).to(dev)
+    tv = torch.stack([torch.from_numpy(b[0]).to(dev) for b in base])[idx].contiguous()
+    tl = torch.stack([torch.from_numpy(b[1]).to(dev) for b in base])[idx].contiguous()
+    tr = torch.stack([torch.from_numpy(b[2]).to(dev) for b in base])[idx].contiguous()
+    out = torch.full((B, H, W), 7, dtype=torch.int16, device=dev)
+    conf = torch.full((B, H, W), -1.0, dtype=torch.float32, device=dev)
+    bf = BatchFilter(True, 8000.0, 1.5, 24, 2, ctx=ctx)
+    bf.filter_device(tl, tv, out, tr, conf, roi)
+    torch.cuda.synchronize()
+    assert tuple(bf.roi) == roi
+    for k in range(NB):                                            # (a) position independence
+        same = idx == k
+        assert bool((out[same] == out[k]).all()) and bool((conf[same] == conf[k]).all())
+    assert bool((out[:, :, :160] == -16).all()) and bool((conf[:, :, :160] == 0).all())   # (c)
+    f = A.createDisparityWLSFilterGeneric(True, ctx=ctx)           # (b) batch == single calls
+    f.setLambda(8000.0); f.setSigmaColor(1.5); f.setLRCthresh(24); f.setDepthDiscontinuityRadius(2)
+    for k in range(NB):
+        single = f.filter(base[k][1], base[k][0], None, base[k][2], roi)
+        assert (out[k].cpu().numpy() == single).all()
+        assert (conf[k].cpu().numpy() == f.getConfidenceMap()).all()
+    ref = O.wls_filter(base[0][1], base[0][0], base[0][2], roi=roi, lam=8000.0, sigma=1.5, lrc_thresh=24, disc_radius=2)
+    assert np.abs(conf[0].cpu().numpy() - ref["conf"]).max() <= 1e-4
+    assert_s16_parity(out[0].cpu().numpy(), ref["out"], roi)
