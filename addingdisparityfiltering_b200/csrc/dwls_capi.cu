@@ -943,12 +943,26 @@ static dwls_status fgs_check(dwls_ctx* ctx, const dwls_image* guide, const dwls_
 template <typename T>
 static void launch_unpack(const dwls_image* src, float* planes, size_t plane, int pitch, cudaStream_t st)
 {
-    unpack_kernel<T><<<dim3((src->cols + 255) / 256, src->rows), 256, 0, st>>>((const T*)src->data, src->step, src->cols, src->channels, planes, plane, pitch);
+    const dim3 grid((src->cols + 1023) / 1024, src->rows);
+    const T* p = (const T*)src->data;
+    switch (src->channels) {
+    case 1: unpack_kernel<T, 1><<<grid, 256, 0, st>>>(p, src->step, src->cols, planes, plane, pitch); break;
+    case 2: unpack_kernel<T, 2><<<grid, 256, 0, st>>>(p, src->step, src->cols, planes, plane, pitch); break;
+    case 3: unpack_kernel<T, 3><<<grid, 256, 0, st>>>(p, src->step, src->cols, planes, plane, pitch); break;
+    default: unpack_kernel<T, 4><<<grid, 256, 0, st>>>(p, src->step, src->cols, planes, plane, pitch); break;
+    }
 }
 template <typename T>
 static void launch_pack(const float* planes, size_t plane, int pitch, dwls_image* dst, cudaStream_t st)
 {
-    pack_kernel<T><<<dim3((dst->cols + 255) / 256, dst->rows), 256, 0, st>>>(planes, plane, pitch, dst->cols, dst->channels, (T*)dst->data, dst->step);
+    const dim3 grid((dst->cols + 1023) / 1024, dst->rows);
+    T* p = (T*)dst->data;
+    switch (dst->channels) {
+    case 1: pack_kernel<T, 1><<<grid, 256, 0, st>>>(planes, plane, pitch, dst->cols, p, dst->step); break;
+    case 2: pack_kernel<T, 2><<<grid, 256, 0, st>>>(planes, plane, pitch, dst->cols, p, dst->step); break;
+    case 3: pack_kernel<T, 3><<<grid, 256, 0, st>>>(planes, plane, pitch, dst->cols, p, dst->step); break;
+    default: pack_kernel<T, 4><<<grid, 256, 0, st>>>(planes, plane, pitch, dst->cols, p, dst->step); break;
+    }
 }
 
 // workspace: chor | cvert | up to 4 planes (+ optional export of the weights)

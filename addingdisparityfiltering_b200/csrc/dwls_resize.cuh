@@ -104,30 +104,77 @@ __global__ void __launch_bounds__(128) upscale_prep_kernel(const UpArgs a)
 }
 
 // ---- standalone FGS: interleaved source -> float planes, float planes -> interleaved dst ------
-// grid = (ceil(w/256), h), S = channels
-template <typename T>
-__global__ void unpack_kernel(const T* __restrict__ src, int64_t sstep_bytes, int w, int cn,
-                              float* __restrict__ planes, int64_t plane_stride, int pitch)
-{
-    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
-    if (j >= w) return;
-    const T* row = (const T*)((const uint8_t*)src + (size_t)i * sstep_bytes) + (size_t)j * cn;
-    for (int ch = 0; ch < cn; ++ch) planes[(size_t)ch * plane_stride + (size_t)i * pitch + j] = (float)row[ch];
-}
-
+// A thread converts 4 consecutive pixels: 4 * CN elements of T = CN * sizeof(T) 32-bit words on the interleaved side (word
+// accesses when the row is 4-byte aligned, element accesses otherwise), one float4 per channel on the plane side (plane rows
+// are padded to a multiple of 8 floats, so whole float4 are always in bounds).  grid = (ceil(w / 1024), h), block 256
 template <typename T> __device__ __forceinline__ T cvt_out(float v);
 template <> __device__ __forceinline__ uint8_t cvt_out<uint8_t>(float v) { return cvt_u8(v); }
 template <> __device__ __forceinline__ int16_t cvt_out<int16_t>(float v) { return cvt_s16(v); }
 template <> __device__ __forceinline__ float cvt_out<float>(float v) { return v; }
 
-template <typename T>
-__global__ void pack_kernel(const float* __restrict__ planes, int64_t plane_stride, int pitch, int w, int cn,
-                            T* __restrict__ dst, int64_t dstep_bytes)
+template <typename T> __device__ __forceinline__ float word_elem(const uint32_t* w, int e);
+template <> __device__ __forceinline__ float word_elem<uint8_t>(const uint32_t* w, int e) { return (float)((w[e >> 2] >> (8 * (e & 3))) & 0xffu); }
+template <> __device__ __forceinline__ float word_elem<int16_t>(const uint32_t* w, int e) { return (float)(short)(w[e >> 1] >> (16 * (e & 1))); }
+template <> __device__ __forceinline__ float word_elem<float>(const uint32_t* w, int e) { return __uint_as_float(w[e]); }
+
+template <typename T, int CN>
+__global__ void __launch_bounds__(256) unpack_kernel(const T* __restrict__ src, int64_t sstep_bytes, int w,
+                                                     float* __restrict__ planes, int64_t plane_stride, int pitch)
 {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
-    if (j >= w) return;
-    T* row = (T*)((uint8_t*)dst + (size_t)i * dstep_bytes) + (size_t)j * cn;
-    for (int ch = 0; ch < cn; ++ch) row[ch] = cvt_out<T>(planes[(size_t)ch * plane_stride + (size_t)i * pitch + j]);
+    constexpr int NW = CN * (int)sizeof(T);                          // words per 4 pixels
+    const int j0 = 4 * (blockIdx.x * blockDim.x + threadIdx.x), i = blockIdx.y;
+    if (j0 >= w) return;
+    const T* row = (const T*)((const uint8_t*)src + (size_t)i * sstep_bytes) + (size_t)j0 * CN;
+    float v[CN][4];
+    if (j0 + 3 < w && (((uintptr_t)row) & 3) == 0) {
+        uint32_t wd[NW];
+#pragma unroll
+        for (int k = 0; k < NW; ++k) wd[k] = __ldg((const uint32_t*)row + k);
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int ch = 0; ch < CN; ++ch) v[ch][q] = word_elem<T>(wd, q * CN + ch);
+    } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int ch = 0; ch < CN; ++ch) v[ch][q] = (j0 + q < w) ? (float)row[q * CN + ch] : 0.f;
+    }
+#pragma unroll
+    for (int ch = 0; ch < CN; ++ch)
+        *(float4*)(planes + (size_t)ch * plane_stride + (size_t)i * pitch + j0) = make_float4(v[ch][0], v[ch][1], v[ch][2], v[ch][3]);
+}
+
+template <typename T, int CN>
+__global__ void __launch_bounds__(256) pack_kernel(const float* __restrict__ planes, int64_t plane_stride, int pitch, int w,
+                                                   T* __restrict__ dst, int64_t dstep_bytes)
+{
+    constexpr int NW = CN * (int)sizeof(T);
+    const int j0 = 4 * (blockIdx.x * blockDim.x + threadIdx.x), i = blockIdx.y;
+    if (j0 >= w) return;
+    T* row = (T*)((uint8_t*)dst + (size_t)i * dstep_bytes) + (size_t)j0 * CN;
+    T o[4 * CN];
+#pragma unroll
+    for (int ch = 0; ch < CN; ++ch) {
+        const float4 f = *(const float4*)(planes + (size_t)ch * plane_stride + (size_t)i * pitch + j0);
+        o[0 * CN + ch] = cvt_out<T>(f.x); o[1 * CN + ch] = cvt_out<T>(f.y); o[2 * CN + ch] = cvt_out<T>(f.z); o[3 * CN + ch] = cvt_out<T>(f.w);
+    }
+    if (j0 + 3 < w && (((uintptr_t)row) & 3) == 0) {
+        uint32_t wd[NW];
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            if (sizeof(T) == 1) wd[k] = (uint32_t)(uint8_t)o[4 * k] | ((uint32_t)(uint8_t)o[4 * k + 1] << 8) | ((uint32_t)(uint8_t)o[4 * k + 2] << 16) | ((uint32_t)(uint8_t)o[4 * k + 3] << 24);
+            else if (sizeof(T) == 2) wd[k] = (uint32_t)(uint16_t)o[2 * k] | ((uint32_t)(uint16_t)o[2 * k + 1] << 16);
+            else wd[k] = __float_as_uint((float)o[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < NW; ++k) ((uint32_t*)row)[k] = wd[k];
+    } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int ch = 0; ch < CN; ++ch) if (j0 + q < w) row[q * CN + ch] = o[q * CN + ch];
+    }
 }
 
 }  // namespace dwls
