@@ -66,6 +66,39 @@ __global__ void __launch_bounds__(128) upscale_prep_kernel(const UpArgs a)
     const int16_t* d1 = a.disp + (size_t)frame * a.d_frame + (size_t)y1 * a.d_step;
     float cval[4] = { 0.f, 0.f, 0.f, 0.f }, dcv[4] = { 0.f, 0.f, 0.f, 0.f };
     bool roi[4];
+    // exactly 2x horizontally (the sample's downscale mode) and away from the image border: the four pixels read source
+    // columns base .. base+3 with the fixed coefficients 0.75 / 0.25 that lin_coeff would produce, so every source value
+    // is loaded once instead of twice and no coefficient arithmetic runs.  Same float operations in the same order.
+    const bool fast2x = (a.W == 2 * a.dw) && X0 >= 1 && X0 + 3 <= a.W - 2;
+    if (fast2x) {
+        const int odd = X0 & 1, base = (X0 >> 1) - 1 + odd;
+        // pixel q takes taps (o, o + 1): even X0 -> (0,1)(1,2)(1,2)(2,3), odd X0 -> (0,1)(0,1)(1,2)(1,2); a1 = 0.75 for even X
+        const float a1e = 0.75f, a1o = 0.25f;
+        float hc0[4], hc1[4], hd0[4], hd1[4];
+        auto taps = [&](auto* r, float (&h)[4]) {
+            const float v0 = (float)r[base], v1 = (float)r[base + 1], v2 = (float)r[base + 2], v3 = odd ? 0.f : (float)r[base + 3];
+            if (!odd) {
+                h[0] = __fadd_rn(__fmul_rn(v0, 1.f - a1e), __fmul_rn(v1, a1e)); h[1] = __fadd_rn(__fmul_rn(v1, 1.f - a1o), __fmul_rn(v2, a1o));
+                h[2] = __fadd_rn(__fmul_rn(v1, 1.f - a1e), __fmul_rn(v2, a1e)); h[3] = __fadd_rn(__fmul_rn(v2, 1.f - a1o), __fmul_rn(v3, a1o));
+            } else {
+                h[0] = __fadd_rn(__fmul_rn(v0, 1.f - a1o), __fmul_rn(v1, a1o)); h[1] = __fadd_rn(__fmul_rn(v0, 1.f - a1e), __fmul_rn(v1, a1e));
+                h[2] = __fadd_rn(__fmul_rn(v1, 1.f - a1o), __fmul_rn(v2, a1o)); h[3] = __fadd_rn(__fmul_rn(v1, 1.f - a1e), __fmul_rn(v2, a1e));
+            }
+        };
+        if (a.conf_lo) { taps(c0, hc0); taps(c1, hc1); }
+        if (any_roi) { taps(d0, hd0); taps(d1, hd1); }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int X = X0 + q;
+            roi[q] = row_in && X >= a.fx && X < a.fx + a.fw;
+            if (a.conf_lo) cval[q] = __fadd_rn(__fmul_rn(hc0[q], b0), __fmul_rn(hc1[q], b1));
+            if (roi[q]) {
+                const int16_t up = cvt_s16(__fadd_rn(__fmul_rn(hd0[q], b0), __fmul_rn(hd1[q], b1)));
+                const float dv = (float)cvt_s16(__fmul_rn((float)up, a.x_ratio));
+                dcv[q] = a.plane_c ? __fmul_rn(cval[q], dv) : dv;
+            }
+        }
+    } else
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         const int X = X0 + q;
