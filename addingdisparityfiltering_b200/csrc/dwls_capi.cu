@@ -8,7 +8,10 @@
 #include <stdlib.h>
 #include <string.h>
 #include <functional>
+#include <algorithm>
+#include <atomic>
 #include <string>
+#include <thread>
 #include <vector>
 #include <unordered_map>
 #include <unordered_set>
@@ -31,6 +34,12 @@ struct dwls_ctx {
     float* lut = nullptr; float lut_sigma = -1.f;           // per-sigma LUT cache (fgs_filter.cpp:150-154)
     void* ws = nullptr; size_t ws_bytes = 0;                // solver workspace (grow-only)
     void* stage = nullptr; size_t stage_bytes = 0;          // device staging of the host entry points
+    // pinned host staging of the single-call entry points: pageable caller memory is copied into it by a few host threads,
+    // each feeding its own copy stream (the driver's own pageable path is single-threaded)
+    void* hpin = nullptr; size_t hpin_bytes = 0;
+    cudaStream_t xs[8] = {};
+    cudaEvent_t xe[8][2] = {};
+    cudaEvent_t xready = nullptr;
     // optional per-kernel CUDA-event timing (bench.py's roofline block)
     bool timing = false;
     struct Span { int id; cudaEvent_t a, b; };
@@ -151,6 +160,12 @@ void dwls_ctx_destroy(dwls_ctx* ctx)
     for (auto& ge : ctx->graph_cache) cudaGraphExecDestroy(ge.exec);
     if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
     cudaFree(ctx->lut); cudaFree(ctx->ws); cudaFree(ctx->stage);
+    if (ctx->hpin) cudaFreeHost(ctx->hpin);
+    for (int t = 0; t < 8; ++t) {
+        if (ctx->xs[t]) cudaStreamDestroy(ctx->xs[t]);
+        for (int k = 0; k < 2; ++k) if (ctx->xe[t][k]) cudaEventDestroy(ctx->xe[t][k]);
+    }
+    if (ctx->xready) cudaEventDestroy(ctx->xready);
     for (auto& sp : ctx->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto e : ctx->free_events) cudaEventDestroy(e);
     delete ctx;
@@ -837,6 +852,127 @@ static bool img_ok(const dwls_image* m, int depth, int cn_a, int cn_b)
 }
 static size_t elem_size(int depth) { return depth == DWLS_8U ? 1 : depth == DWLS_16S ? 2 : 4; }
 
+// ---------------------------------------------------------------------------------------------
+// host <-> device transfers of the single-call entry points.  A job moves `rows` rows of `row_bytes` between caller memory
+// (any row step, normally pageable) and a dense device array.  Small transfers go through the driver's pageable path on the
+// launching stream; larger ones through pinned staging, split into row slabs over XFER_T host threads, each with its own
+// copy stream, a slab moving in chunks so that the host-side memcpy of one chunk overlaps the DMA of another.
+// ---------------------------------------------------------------------------------------------
+struct XferJob { uint8_t* host; int64_t hstep; size_t row_bytes; int rows; uint8_t* dev; size_t pin_off; };
+static const int XFER_T = 4;
+static const size_t XFER_MIN = (size_t)2 << 20, XFER_CHUNK = (size_t)1 << 20;
+
+static dwls_status xfer_prepare(dwls_ctx* ctx, XferJob* jobs, int n, size_t* total)
+{
+    size_t off = 0;
+    for (int i = 0; i < n; ++i) { jobs[i].pin_off = off; off += align256(jobs[i].row_bytes * jobs[i].rows); }
+    *total = off;
+    if (off < XFER_MIN) return DWLS_OK;
+    if (ctx->hpin_bytes < off) {
+        if (ctx->hpin) { cudaFreeHost(ctx->hpin); ctx->hpin = nullptr; ctx->hpin_bytes = 0; }
+        CK(cudaHostAlloc(&ctx->hpin, off, cudaHostAllocDefault));
+        ctx->hpin_bytes = off;
+    }
+    for (int t = 0; t < XFER_T; ++t) {
+        if (!ctx->xs[t]) CK(cudaStreamCreateWithFlags(&ctx->xs[t], cudaStreamNonBlocking));
+        for (int k = 0; k < 2; ++k) if (!ctx->xe[t][k]) CK(cudaEventCreateWithFlags(&ctx->xe[t][k], cudaEventDisableTiming));
+    }
+    if (!ctx->xready) CK(cudaEventCreateWithFlags(&ctx->xready, cudaEventDisableTiming));
+    return DWLS_OK;
+}
+
+// rows [r0, r1) of a job between caller memory and the pinned buffer
+static void xfer_rows(const XferJob& j, uint8_t* pin, int r0, int r1, bool to_pin)
+{
+    uint8_t* p = pin + j.pin_off + (size_t)r0 * j.row_bytes;
+    uint8_t* h = j.host + (size_t)r0 * j.hstep;
+    if (j.hstep == (int64_t)j.row_bytes) { if (to_pin) memcpy(p, h, (size_t)(r1 - r0) * j.row_bytes); else memcpy(h, p, (size_t)(r1 - r0) * j.row_bytes); return; }
+    for (int r = r0; r < r1; ++r, p += j.row_bytes, h += j.hstep) { if (to_pin) memcpy(p, h, j.row_bytes); else memcpy(h, p, j.row_bytes); }
+}
+
+// host -> device; on return the copies are queued and `st` waits for them
+static dwls_status xfer_upload(dwls_ctx* ctx, XferJob* jobs, int n, cudaStream_t st)
+{
+    size_t total = 0;
+    dwls_status s = xfer_prepare(ctx, jobs, n, &total);
+    if (s) return s;
+    if (total < XFER_MIN) {
+        for (int i = 0; i < n; ++i)
+            CK(cudaMemcpy2DAsync(jobs[i].dev, jobs[i].row_bytes, jobs[i].host, (size_t)jobs[i].hstep, jobs[i].row_bytes, jobs[i].rows, cudaMemcpyHostToDevice, st));
+        return DWLS_OK;
+    }
+    std::atomic<int> err(0);
+    auto work = [&](int t) {
+        if (cudaSetDevice(ctx->device) != cudaSuccess) { err = 1; return; }
+        for (int i = 0; i < n; ++i) {
+            const XferJob& j = jobs[i];
+            const int r0 = (int)((int64_t)j.rows * t / XFER_T), r1 = (int)((int64_t)j.rows * (t + 1) / XFER_T);
+            const int step = (int)std::max<size_t>(1, XFER_CHUNK / j.row_bytes);
+            for (int r = r0; r < r1; r += step) {
+                const int re = std::min(r + step, r1);
+                xfer_rows(j, (uint8_t*)ctx->hpin, r, re, true);
+                if (cudaMemcpyAsync(j.dev + (size_t)r * j.row_bytes, (uint8_t*)ctx->hpin + j.pin_off + (size_t)r * j.row_bytes, (size_t)(re - r) * j.row_bytes,
+                                    cudaMemcpyHostToDevice, ctx->xs[t]) != cudaSuccess) { err = 1; return; }
+            }
+        }
+        if (cudaEventRecord(ctx->xe[t][0], ctx->xs[t]) != cudaSuccess) err = 1;
+    };
+    std::thread th[XFER_T - 1];
+    for (int t = 1; t < XFER_T; ++t) th[t - 1] = std::thread(work, t);
+    work(0);
+    for (int t = 1; t < XFER_T; ++t) th[t - 1].join();
+    if (err) { cudaGetLastError(); return fail(ctx, DWLS_CUDA_ERROR, "host-to-device staging copy failed"); }
+    for (int t = 0; t < XFER_T; ++t) CK(cudaStreamWaitEvent(st, ctx->xe[t][0], 0));
+    return DWLS_OK;
+}
+
+// device -> host after everything queued on `st`; returns when the caller's buffers are filled
+static dwls_status xfer_download(dwls_ctx* ctx, XferJob* jobs, int n, cudaStream_t st)
+{
+    size_t total = 0;
+    dwls_status s = xfer_prepare(ctx, jobs, n, &total);
+    if (s) return s;
+    if (total < XFER_MIN) {
+        for (int i = 0; i < n; ++i)
+            CK(cudaMemcpy2DAsync(jobs[i].host, (size_t)jobs[i].hstep, jobs[i].dev, jobs[i].row_bytes, jobs[i].row_bytes, jobs[i].rows, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        return DWLS_OK;
+    }
+    CK(cudaEventRecord(ctx->xready, st));
+    std::atomic<int> err(0);
+    auto work = [&](int t) {
+        if (cudaSetDevice(ctx->device) != cudaSuccess || cudaStreamWaitEvent(ctx->xs[t], ctx->xready, 0) != cudaSuccess) { err = 1; return; }
+        // the chunks of this thread's slabs, two in flight: chunk c+1 is being copied while chunk c is moved to the caller
+        struct Chunk { int job, r0, r1; };
+        std::vector<Chunk> ch;
+        for (int i = 0; i < n; ++i) {
+            const XferJob& j = jobs[i];
+            const int r0 = (int)((int64_t)j.rows * t / XFER_T), r1 = (int)((int64_t)j.rows * (t + 1) / XFER_T);
+            const int step = (int)std::max<size_t>(1, XFER_CHUNK / j.row_bytes);
+            for (int r = r0; r < r1; r += step) ch.push_back({ i, r, std::min(r + step, r1) });
+        }
+        auto issue = [&](size_t c) {
+            const XferJob& j = jobs[ch[c].job];
+            const size_t off = (size_t)ch[c].r0 * j.row_bytes;
+            if (cudaMemcpyAsync((uint8_t*)ctx->hpin + j.pin_off + off, j.dev + off, (size_t)(ch[c].r1 - ch[c].r0) * j.row_bytes, cudaMemcpyDeviceToHost, ctx->xs[t]) != cudaSuccess ||
+                cudaEventRecord(ctx->xe[t][c & 1], ctx->xs[t]) != cudaSuccess) err = 1;
+        };
+        if (!ch.empty()) issue(0);
+        for (size_t c = 0; c < ch.size() && !err; ++c) {
+            if (cudaEventSynchronize(ctx->xe[t][c & 1]) != cudaSuccess) { err = 1; break; }
+            if (c + 1 < ch.size()) issue(c + 1);
+            xfer_rows(jobs[ch[c].job], (uint8_t*)ctx->hpin, ch[c].r0, ch[c].r1, false);
+        }
+    };
+    std::thread th[XFER_T - 1];
+    for (int t = 1; t < XFER_T; ++t) th[t - 1] = std::thread(work, t);
+    work(0);
+    for (int t = 1; t < XFER_T; ++t) th[t - 1].join();
+    if (err) { cudaGetLastError(); return fail(ctx, DWLS_CUDA_ERROR, "device-to-host staging copy failed"); }
+    CK(cudaStreamSynchronize(st));
+    return DWLS_OK;
+}
+
 static dwls_status filter_host_impl(dwls_ctx* ctx, const dwls_image* dl, const dwls_image* dr, const dwls_image* view,
                                     const int* roi_in, const dwls_params* p, dwls_image* out, dwls_image* conf, int* roi_out,
                                     uint8_t* mask, int64_t mask_step, int mask_view_cols)
@@ -878,9 +1014,18 @@ static dwls_status filter_host_impl(dwls_ctx* ctx, const dwls_image* dl, const d
     uint8_t* d_conf = d_out + b_out; uint8_t* d_mask = d_conf + b_conf;
     ctx->h2d_bytes += (int64_t)dw * dh * 2 * (useconf ? 2 : 1) + (mask_only ? 0 : (int64_t)W * H * vcn);
     ctx->d2h_bytes += mask_only ? (int64_t)dw * dh : (int64_t)W * H * 2 + (want_conf ? (int64_t)W * H * 4 : 0);
-    CK(cudaMemcpy2DAsync(d_dl, (size_t)dw * 2, dl->data, dl->step, (size_t)dw * 2, dh, cudaMemcpyHostToDevice, st));
-    if (useconf) CK(cudaMemcpy2DAsync(d_dr, (size_t)dw * 2, dr->data, dr->step, (size_t)dw * 2, dh, cudaMemcpyHostToDevice, st));
-    if (!mask_only) CK(cudaMemcpy2DAsync(d_view, (size_t)W * vcn, view->data, view->step, (size_t)W * vcn, H, cudaMemcpyHostToDevice, st));
+    XferJob in[3], outj[2];
+    int n_in = 0, n_out = 0;
+    in[n_in++] = { (uint8_t*)dl->data, dl->step, (size_t)dw * 2, dh, d_dl, 0 };
+    if (useconf) in[n_in++] = { (uint8_t*)dr->data, dr->step, (size_t)dw * 2, dh, d_dr, 0 };
+    if (!mask_only) {
+        in[n_in++] = { (uint8_t*)view->data, view->step, (size_t)W * vcn, H, d_view, 0 };
+        outj[n_out++] = { (uint8_t*)out->data, out->step, (size_t)W * 2, H, d_out, 0 };
+        if (want_conf) outj[n_out++] = { (uint8_t*)conf->data, conf->step, (size_t)W * 4, H, d_conf, 0 };
+        size_t reserve = 0;
+        if ((s = xfer_prepare(ctx, outj, n_out, &reserve))) return s;      // the pinned buffer must not grow between upload and download
+    }
+    if ((s = xfer_upload(ctx, in, n_in, st))) return s;
     dwls_batch b;
     memset(&b, 0, sizeof b);
     b.n_frames = 1;
@@ -901,10 +1046,7 @@ static dwls_status filter_host_impl(dwls_ctx* ctx, const dwls_image* dl, const d
     }
     if ((s = ensure_lut(ctx, (float)p->sigma_color, st))) return s;
     if ((s = filter_frames_graphed(ctx, &b, 0, 1, g, p, roi_in, st))) return s;
-    CK(cudaMemcpy2DAsync(out->data, out->step, d_out, (size_t)W * 2, (size_t)W * 2, H, cudaMemcpyDeviceToHost, st));
-    if (want_conf) CK(cudaMemcpy2DAsync(conf->data, conf->step, d_conf, (size_t)W * 4, (size_t)W * 4, H, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    return DWLS_OK;
+    return xfer_download(ctx, outj, n_out, st);
 }
 
 extern "C" dwls_status dwls_filter_host(dwls_ctx* ctx, const dwls_image* dl, const dwls_image* dr, const dwls_image* view,
@@ -1043,14 +1185,13 @@ extern "C" dwls_status dwls_fgs_host(dwls_ctx* ctx, const dwls_image* guide, con
     uint8_t* d_g = (uint8_t*)ctx->stage; uint8_t* d_s = d_g + b_g; uint8_t* d_d = d_s + b_s;
     ctx->h2d_bytes += (int64_t)(grow + srow) * h;
     ctx->d2h_bytes += (int64_t)srow * h;
-    CK(cudaMemcpy2DAsync(d_g, grow, guide->data, guide->step, grow, h, cudaMemcpyHostToDevice, st));
-    CK(cudaMemcpy2DAsync(d_s, srow, src->data, src->step, srow, h, cudaMemcpyHostToDevice, st));
+    XferJob in[2] = { { (uint8_t*)guide->data, guide->step, grow, h, d_g, 0 }, { (uint8_t*)src->data, src->step, srow, h, d_s, 0 } };
+    XferJob outj[1] = { { (uint8_t*)dst->data, dst->step, srow, h, d_d, 0 } };
+    if ((s = xfer_upload(ctx, in, 2, st))) return s;          // in >= out: the pinned buffer does not grow again for the download
     dwls_image G = *guide, Sm = *src, D = *dst;
     G.data = d_g; G.step = (int64_t)grow; Sm.data = d_s; Sm.step = (int64_t)srow; D.data = d_d; D.step = (int64_t)srow;
     if ((s = fgs_dev_impl(ctx, &G, &Sm, &D, lambda, sigma, att, num_iter, st, nullptr, nullptr))) return s;
-    CK(cudaMemcpy2DAsync(dst->data, dst->step, d_d, srow, srow, h, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    return DWLS_OK;
+    return xfer_download(ctx, outj, 1, st);
 }
 
 extern "C" dwls_status dwls_fgs_weights_host(dwls_ctx* ctx, const dwls_image* guide, double sigma, float* chor, float* cvert)
