@@ -102,7 +102,9 @@ DWLS_API dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames);
  * disparity-map coordinates or NULL / zero area to derive it from the offsets (228-233).
  * out16s: CV_16SC1 at view size, caller-allocated.  conf32f: optional CV_32FC1 at view size
  * (getConfidenceMap, 138/274).  roi_out: the disparity-resolution ROI used (getROI, 139).
- * Copies H2D, runs the kernels, copies D2H, synchronises. */
+ * Copies H2D, runs the kernels, copies D2H, synchronises.  The buffers may be ordinary pageable memory: transfers of more
+ * than 2 MB are staged through pinned memory by four short-lived host threads of the library (each with its own copy
+ * stream); smaller ones take the driver's pageable path.  dwls_fgs_host moves its images the same way. */
 DWLS_API dwls_status dwls_filter_host(dwls_ctx* ctx,
                                       const dwls_image* disp_left, const dwls_image* disp_right,
                                       const dwls_image* view, const int* roi_in, const dwls_params* params,
