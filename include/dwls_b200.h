@@ -90,9 +90,10 @@ DWLS_API int64_t     dwls_graph_replays(const dwls_ctx* ctx);
  * dwls_filter_batch_host uploads only the part of each input the filter reads: the ROI of the left disparity map and of
  * the view, the mirrored ROI of the right disparity map (disparity_filters.cpp:202-203), each with a few pixels of margin. */
 DWLS_API void        dwls_transfer_bytes(const dwls_ctx* ctx, int64_t* h2d, int64_t* d2h);
-/* layout of the two solver planes of the confidence path between the sweeps (on by default): one array interleaved
- * sector by sector, so that a column strip of both planes is 64 contiguous bytes per row; off = two row-major planes.
- * Results are identical either way; the switch exists for A/B measurements and tests. */
+/* layout of the two solver planes of the confidence path between the sweeps: off (the default) = two row-major planes;
+ * on = one array interleaved sector by sector, so that a column strip of both planes is 64 contiguous bytes per row
+ * (faster column pass, slower row pass: measured a net loss).  Results are identical either way; the
+ * switch exists for A/B measurements and tests. */
 DWLS_API dwls_status dwls_set_plane_interleave(dwls_ctx* ctx, int on);
 /* frames processed per kernel launch group in the batch entry point (0 = choose automatically) */
 DWLS_API dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames);
