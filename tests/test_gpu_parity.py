@@ -353,3 +353,44 @@ def test_wls_zero_confidence_regions_next_to_sharp_edges(ctx):
     ref = O.wls_filter(dl, view, dr, roi=roi, lam=8000.0, sigma=1.5, disc_radius=2)
     assert (ref["out"][:, 32:] == -32768).mean() > 0.3          # the case really exercises the overflow range
     print("zero-confidence regions parity", st)
+
+
+def test_large_strided_host_images_take_the_staged_transfer_path(ctx):
+    """Host images above 2 MB travel through pinned staging filled by several host threads (dwls_filter_host / dwls_fgs_host).
+    Row-strided inputs and outputs (cv::Mat ROI views inside larger allocations), passed straight to the C-ABI, must give
+    the same bytes as dense ones."""
+    import ctypes as C
+    from addingdisparityfiltering_b200 import _lib
+    from addingdisparityfiltering_b200.ximgproc import _params
+    w, h = 1280, 720
+    view, dl, dr, roi = synth.make_artificial_example(w, h, 3, seed=77)
+
+    def strided(a, pad):
+        big = np.zeros((a.shape[0] + 3, a.shape[1] + 5 + pad) + a.shape[2:], a.dtype)
+        v = big[2:2 + a.shape[0], 5:5 + a.shape[1]]
+        v[...] = a
+        assert not v.flags["C_CONTIGUOUS"]
+        return v
+
+    def run(dl_, dr_, view_, out_, conf_):
+        p = _params(8000.0, 1.5, 24, 3, (0, 0, 0, 0), True)
+        imgs = [_lib.image_of(x) for x in (dl_, dr_, view_, out_, conf_)]
+        roi_in, roi_out = (C.c_int * 4)(*roi), (C.c_int * 4)()
+        ctx.check(_lib.lib().dwls_filter_host(ctx.handle, C.byref(imgs[0]), C.byref(imgs[1]), C.byref(imgs[2]), roi_in, C.byref(p),
+                                              C.byref(imgs[3]), C.byref(imgs[4]), roi_out))
+    out_d, conf_d = np.zeros((h, w), np.int16), np.zeros((h, w), np.float32)
+    run(dl, dr, view, out_d, conf_d)
+    out_s, conf_s = strided(np.zeros((h, w), np.int16), 11), strided(np.zeros((h, w), np.float32), 3)
+    run(strided(dl, 9), strided(dr, 13), strided(view, 7), out_s, conf_s)
+    assert (out_s == out_d).all() and (conf_s == conf_d).all()
+    ref = O.wls_filter(dl, view, dr, roi=roi, lam=8000.0, sigma=1.5, disc_radius=3)
+    assert np.abs(conf_d - ref["conf"]).max() <= 1e-4
+    assert_s16_parity(out_d, ref["out"], roi)
+    # standalone FGS, 8UC3 source of 2.7 MB: dense vs strided guide / source / destination
+    lib = _lib.lib()
+    dst_d, dst_s = np.zeros_like(view), strided(np.zeros_like(view), 5)
+    g_s, s_s = strided(view, 7), strided(view, 3)
+    for g_, s_, d_ in ((view, view, dst_d), (g_s, s_s, dst_s)):
+        ig, is_, id_ = _lib.image_of(g_), _lib.image_of(s_), _lib.image_of(d_)
+        ctx.check(lib.dwls_fgs_host(ctx.handle, C.byref(ig), C.byref(is_), C.byref(id_), C.c_double(1000.0), C.c_double(10.0), C.c_double(0.25), 3))
+    assert (dst_d == dst_s).all()
