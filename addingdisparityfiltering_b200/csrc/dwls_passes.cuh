@@ -140,6 +140,7 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : 2) : 1
         mbar_fence_init();
     }
     __syncthreads();
+    const int tma_thread = K > 32 ? 32 : 0;
     int frame = (int)blockIdx.x / a.h, row = (int)blockIdx.x - frame * a.h;
     int pframe = frame, prow = row;                               // the row HST ahead (the one whose fetch is issued next)
     for (int i = 0; i < HST; ++i) {
@@ -210,7 +211,7 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : 2) : 1
             for (int s = 0; s < S; ++s) Fd[s * KP + p] = 0.f;
         }
         __syncthreads();                       // level-2 rows complete; every thread is done reading this stage
-        if (t == 0 && i + HST < n_mine) issue(i + HST, pframe, prow);
+        if (t == tma_thread && i + HST < n_mine) issue(i + HST, pframe, prow);      // not the level-2 warp: its solve is the serial section
         pframe += step_f; prow += step_r;
         if (prow >= a.h) { prow -= a.h; ++pframe; }
         if (t < 32) {
@@ -302,6 +303,7 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
     float* A = l2base + x * SYS; float* B = A + KP; float* Bd = B + KP; float* C = Bd + KP;
     float* F = C + KP; float* Fd = F + S * KP;
     const int n_mine = (g.strips_total - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int tma_thread = ((int)blockDim.x > 32 * VC) ? 32 * VC : 0;
     const uint32_t tx_bytes = (uint32_t)(((WB ? 0 : rows_staged) + S * rows_staged) * VC * sizeof(float));
 
     // my i-th strip is number blockIdx.x + i * gridDim.x; its (frame, strip in the frame) advance by a constant step
@@ -380,7 +382,9 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
             for (int s = 0; s < S; ++s) Fd[s * KP + p] = 0.f;
         }
         __syncthreads();                       // level-2 rows complete; the stage has been read by everyone
-        if (t == 0 && i + 1 < n_mine) issue(nframe, nstrip);
+        // the next strip's tiles are requested by the first thread that is NOT in a level-2 warp: the dozen TMA instructions
+        // would otherwise sit at the head of system 0's solve, the serial section every other warp is waiting for
+        if (t == tma_thread && i + 1 < n_mine) issue(nframe, nstrip);
         {
             const int warp = t >> 5, nwarps = blockDim.x >> 5, lane = t & 31;
             if (warp < VC) {
