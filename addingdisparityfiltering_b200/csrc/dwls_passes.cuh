@@ -296,6 +296,7 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
     float* stash = l2base + (size_t)VC * SYS;                      // [(2+S)*M][32*VC]: level-2 warps park their level-1 state
     uint64_t* full = (uint64_t*)(stash + (size_t)VC * 32 * (2 + S) * M);
     uint64_t* wfull = full + 1;                                   // [2]
+    uint64_t* udone = full + 3;                                   // every thread arrives once it has read its level-2 results
     const int t = threadIdx.x, x = t % VC, k = t / VC, r0 = k * M;
     // interleaved planes: every other pair of chunks holds plane 1 in f[0] and plane 0 in f[1], so that the four chunks of a
     // warp read four different bank groups of the [row][plane][VC] stage
@@ -325,7 +326,7 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
         bulk_g2s(wstage + (size_t)(i & 1) * rows_staged * VC, a.weight + (size_t)frame * a.w_frame + (size_t)strip * ((size_t)a.h * VC), bytes, wfull + (i & 1));
     };
 
-    if (t == 0) { mbar_init(full, 1); mbar_init(wfull, 1); mbar_init(wfull + 1, 1); mbar_fence_init(); }
+    if (t == 0) { mbar_init(full, 1); mbar_init(wfull, 1); mbar_init(wfull + 1, 1); mbar_init(udone, blockDim.x); mbar_fence_init(); }
     __syncthreads();
     int frame = (int)blockIdx.x / g.strips_x, strip = (int)blockIdx.x - frame * g.strips_x;
     if (t == 0 && n_mine > 0) { if (WB) issue_w(0, frame, strip); issue(frame, strip); }
@@ -367,6 +368,7 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
         }
         const Level1Out<M, S> o = level1_reduce<M, S>(c, f, v, aprev);
         const int p = l2pad(k);
+        if (i > 0) mbar_wait(udone, (uint32_t)((i - 1) & 1));
         A[p] = o.A; B[p] = o.B;
 #pragma unroll
         for (int s = 0; s < S; ++s) F[(s ^ sel) * KP + p] = o.Fs[s];
@@ -412,7 +414,8 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
         float Uown[S], Uprev[S];
 #pragma unroll
         for (int s = 0; s < S; ++s) { Uown[s] = F[(s ^ sel) * KP + p]; Uprev[s] = (k > 0) ? F[(s ^ sel) * KP + l2pad(k - 1)] : 0.f; }
-        __syncthreads();                       // level-2 scratch may be overwritten by the next strip from here on
+        mbar_arrive(udone);                    // split barrier: the level-2 scratch may be overwritten once everybody has arrived,
+                                               // which the next strip checks just before it writes there (nobody waits here)
         level1_fixup<M, S>(c, f, v, Uprev, Uown);
         constexpr bool PAIR = (FIN == FIN_FLOAT && S == 2 && !IL && VC % 2 == 0 && M % 2 == 1);
         if (PAIR) {
