@@ -23,10 +23,56 @@ def _strides_bytes(t):
     return [int(s) for s in t.strides]
 
 
-def _make_batch(disp_left, disp_right, view, out, conf):
+def _bad(msg):
+    raise _lib.DwlsError(_lib.DWLS_BAD_ARG, msg)
+
+
+def _is_torch(t):
+    return hasattr(t, "data_ptr")
+
+
+def _dtype_name(t):
+    return str(t.dtype).replace("torch.", "")
+
+
+def _check_array(name, t, dtype, shape, on_device, device_index):
+    """The checks image_of() makes for single frames, for one array of a batch: dtype, rank, shape, pixels of a row
+    contiguous, non-negative strides, placement (CUDA tensor on the ctx's device / host memory)."""
+    if _dtype_name(t) != dtype:
+        _bad("%s must be %s, got %s" % (name, dtype, _dtype_name(t)))
+    if tuple(t.shape) != tuple(shape):
+        _bad("%s must have shape %s, got %s" % (name, tuple(shape), tuple(t.shape)))
+    st = _strides_bytes(t)
+    es = t.element_size() if _is_torch(t) else t.itemsize
+    px = es * (t.shape[3] if len(t.shape) == 4 else 1)             # bytes per pixel
+    if st[2] != px or (len(t.shape) == 4 and st[3] != es):
+        _bad("%s: the pixels of a row must be contiguous" % name)
+    if (t.shape[1] > 1 and st[1] < px * t.shape[2]) or (t.shape[0] > 1 and st[0] < st[1] * (t.shape[1] - 1) + px * t.shape[2]):
+        _bad("%s: rows and frames must not overlap (positive strides, frame after frame)" % name)
+    if on_device:
+        if not (_is_torch(t) and t.is_cuda):
+            _bad("%s must be a CUDA tensor" % name)
+        if t.device.index != device_index:
+            _bad("%s lives on cuda:%s but the context owns cuda:%s" % (name, t.device.index, device_index))
+    elif _is_torch(t) and t.is_cuda:
+        _bad("%s must be host memory (numpy array or pinned torch tensor)" % name)
+
+
+def _make_batch(disp_left, disp_right, view, out, conf, on_device=False, device_index=0):
+    if len(disp_left.shape) != 3 or disp_left.shape[0] <= 0:
+        _bad("disp_left must be [n, rows, cols] with n > 0")
+    if len(view.shape) not in (3, 4) or (len(view.shape) == 4 and view.shape[3] not in (1, 3)):
+        _bad("view must be [n, H, W] or [n, H, W, 1 or 3]")
     n, dh, dw = disp_left.shape
     H, W = view.shape[1], view.shape[2]
-    cn = 1 if view.ndim == 3 else view.shape[3]
+    cn = 1 if len(view.shape) == 3 else view.shape[3]
+    _check_array("disp_left", disp_left, "int16", (n, dh, dw), on_device, device_index)
+    if disp_right is not None:
+        _check_array("disp_right", disp_right, "int16", (n, dh, dw), on_device, device_index)      # disparity_filters.cpp:263-264
+    _check_array("view", view, "uint8", (n, H, W) if len(view.shape) == 3 else (n, H, W, cn), on_device, device_index)
+    _check_array("out", out, "int16", (n, H, W), on_device, device_index)
+    if conf is not None:
+        _check_array("conf", conf, "float32", (n, H, W), on_device, device_index)
     b = Batch()
     b.n_frames = n
     sl = _strides_bytes(disp_left)
@@ -72,7 +118,7 @@ class BatchFilter:
             stream = torch.cuda.current_stream(disp_left.device).cuda_stream
         if not stream:
             stream = 1          # cudaStreamLegacy: torch's default stream, not the ctx's private one
-        b = _make_batch(disp_left, disp_right, view, out, conf)
+        b = _make_batch(disp_left, disp_right, view, out, conf, on_device=True, device_index=self.ctx.device)
         self._call(_lib.lib().dwls_filter_batch_dev, b, ROI, C.c_void_p(stream))
         return out
 
@@ -100,3 +146,116 @@ def gather_results(local_out, group=None):
     # gathered as raw bytes: the collective only moves data, and gloo has no int16 kernels
     dist.all_gather_into_tensor(full.view(torch.uint8), local_out.contiguous().view(torch.uint8), group=group)
     return full
+
+
+def chunk_plan(n_local, chunk, tail_min=0):
+    """Splits a shard of n_local frames into launch / gather chunks [(first, count)]: `chunk` frames each; with tail_min > 0
+    the last chunk is halved repeatedly down to tail_min frames, because the gather of the LAST chunk is the only one
+    that is not hidden behind the next chunk's kernels."""
+    plan, f = [], 0
+    while n_local - f > chunk:
+        plan.append((f, chunk))
+        f += chunk
+    left = n_local - f
+    while tail_min > 0 and left > tail_min:
+        nf = (left + 1) // 2
+        plan.append((f, nf))
+        f += nf
+        left -= nf
+    if left > 0:
+        plan.append((f, left))
+    return plan
+
+
+class ShardedBatch:
+    """A batch of n_total independent frames sharded over the ranks of a process group (contiguous blocks,
+    shard_frames), filtered chunk by chunk, with the CV_16S results gathered over NCCL WHILE the next chunk is computed.
+
+    mode "root": grouped ncclSend / ncclRecv to rank `dst` (every byte crosses NVLink once: (world-1)/world of the batch
+    enters the root, each other rank only reads its own shard); mode "all": every rank ends up with the whole batch
+    (grouped send/recv between all pairs, (world-1) x the bytes).  The collective of chunk k is issued right after the
+    kernels of chunk k: torch's NCCL stream waits for them through an event and runs beside the kernels of chunk k+1 that
+    are launched next on the compute stream; wait() joins the two streams at the end of the step.  The receives land
+    directly at their final position in `full` (frame order of the unsharded batch) - no staging copy, no reorder pass;
+    a rank's own shard is a view of `full`, so the root's own results need no copy either."""
+
+    def __init__(self, n_total, frame_shape, chunk=16, tail_min=4, mode="root", dst=0, group=None, device=None, dtype=None):
+        import torch
+        import torch.distributed as dist
+        self.dist = dist if dist.is_available() and dist.is_initialized() else None
+        self.group = group
+        self.world = self.dist.get_world_size(group) if self.dist else 1
+        self.rank = self.dist.get_rank(group) if self.dist else 0
+        self.n_total, self.mode, self.dst = n_total, mode, dst
+        self.spans = [shard_frames(n_total, self.world, r) for r in range(self.world)]
+        self.begin, self.end = self.spans[self.rank]
+        self.plans = [chunk_plan(e - b, chunk, tail_min) for b, e in self.spans]      # every rank can derive every peer's plan
+        self.plan = self.plans[self.rank]
+        holds_all = self.world == 1 or mode == "all" or self.rank == dst
+        dtype = dtype or torch.int16
+        n_alloc = n_total if holds_all else self.end - self.begin
+        self.full = torch.empty((n_alloc,) + tuple(frame_shape), dtype=dtype, device=device)
+        self.local = self.full[self.begin:self.end] if holds_all else self.full
+        self.holds_all = holds_all
+        self._works = []
+        self.bytes_sent = 0
+
+    def _wire(self, t):
+        # the collective only moves bytes (NCCL has no int16 type, gloo no int16 kernels)
+        import torch
+        return t.view(torch.uint8).view(-1)
+
+    def _frames_of(self, r, k):
+        b = self.spans[r][0]
+        f0, nf = self.plans[r][k]
+        return self._wire(self.full[b + f0:b + f0 + nf])
+
+    def gather_chunk(self, k):
+        """Queues the collective for my k-th chunk (and, on receiving ranks, the k-th chunk of every peer that has one)."""
+        if self.world == 1:
+            return
+        dist = self.dist
+        ops = []
+        f0, nf = self.plan[k] if k < len(self.plan) else (0, 0)
+        mine = self._wire(self.local[f0:f0 + nf]) if nf else None
+        if self.mode == "root":
+            if self.rank == self.dst:
+                ops = [dist.P2POp(dist.irecv, self._frames_of(r, k), r, self.group) for r in range(self.world)
+                       if r != self.dst and k < len(self.plans[r])]
+            elif nf:
+                ops = [dist.P2POp(dist.isend, mine, self.dst, self.group)]
+                self.bytes_sent += mine.numel() * mine.element_size()
+        else:
+            for r in range(self.world):
+                if r == self.rank:
+                    continue
+                if nf:
+                    ops.append(dist.P2POp(dist.isend, mine, r, self.group))
+                    self.bytes_sent += mine.numel() * mine.element_size()
+                if k < len(self.plans[r]):
+                    ops.append(dist.P2POp(dist.irecv, self._frames_of(r, k), r, self.group))
+        if ops:
+            self._works += dist.batch_isend_irecv(ops)
+
+    @property
+    def n_chunks(self):
+        return max(len(p) for p in self.plans)
+
+    def wait(self):
+        """Joins the communication stream into the caller's stream (GPU) / blocks until the transfers are done (CPU)."""
+        for w in self._works:
+            w.wait()
+        self._works = []
+
+    def run(self, filter_chunk, gather=True):
+        """filter_chunk(first_local_frame, count, out_view) computes one chunk into out_view (asynchronously on the current
+        stream); chunks of peers that are longer than mine still need my receives, hence n_chunks."""
+        for k in range(self.n_chunks):
+            if k < len(self.plan):
+                f0, nf = self.plan[k]
+                filter_chunk(f0, nf, self.local[f0:f0 + nf])
+            if gather:
+                self.gather_chunk(k)
+        if gather:
+            self.wait()
+        return self.full

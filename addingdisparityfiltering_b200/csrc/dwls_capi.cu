@@ -10,6 +10,7 @@
 #include <functional>
 #include <algorithm>
 #include <atomic>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -59,7 +60,24 @@ struct dwls_ctx {
     struct HCache { int ctas_per_sm = 0, K = 0; size_t smem = 0; };
     std::unordered_map<const void*, HCache> hcache;          // row-pass occupancy, by kernel instance
     std::unordered_set<const void*> smem_attr_done;          // kernels whose dynamic shared-memory limit has been raised
+    // Calls share the workspace, the LUT and the cached graphs, so two calls on DIFFERENT streams must not overlap: every
+    // device entry point records `busy` on its stream when it has queued its work, and the next one waits for it when it
+    // runs on another stream (same stream: already ordered).
+    cudaEvent_t busy = nullptr; cudaStream_t busy_stream = nullptr; bool busy_valid = false;
 };
+
+// orders a call on `st` after the previous call's work (see dwls_ctx::busy)
+static cudaError_t call_enter(dwls_ctx* ctx, cudaStream_t st)
+{
+    if (ctx->busy_valid && ctx->busy_stream != st) return cudaStreamWaitEvent(st, ctx->busy, 0);
+    return cudaSuccess;
+}
+static cudaError_t call_leave(dwls_ctx* ctx, cudaStream_t st)
+{
+    if (!ctx->busy) { cudaError_t e = cudaEventCreateWithFlags(&ctx->busy, cudaEventDisableTiming); if (e != cudaSuccess) return e; }
+    ctx->busy_stream = st; ctx->busy_valid = true;
+    return cudaEventRecord(ctx->busy, st);
+}
 
 enum KernelId { K_LUT = 0, K_WEIGHTS, K_CONF_R, K_CONF_L, K_UPSCALE, K_PREP, K_FILL, K_HSOLVE, K_VSOLVE, K_VSOLVE_FIN, K_UNPACK, K_PACK, K_TRANSPOSE, K_COUNT };
 static const char* const kKernelNames[K_COUNT] = { "lut_kernel", "weights_kernel", "conf_kernel<right>", "conf_kernel<left+lrc>", "upscale_prep_kernel",
@@ -166,6 +184,7 @@ void dwls_ctx_destroy(dwls_ctx* ctx)
         for (int k = 0; k < 2; ++k) if (ctx->xe[t][k]) cudaEventDestroy(ctx->xe[t][k]);
     }
     if (ctx->xready) cudaEventDestroy(ctx->xready);
+    if (ctx->busy) cudaEventDestroy(ctx->busy);
     for (auto& sp : ctx->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto e : ctx->free_events) cudaEventDestroy(e);
     delete ctx;
@@ -311,17 +330,23 @@ static dwls_status launch_h(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static EncodeTiledFn g_encode = nullptr;
+static std::once_flag g_encode_once;
+// resolved once per process (contexts may be created and used from several threads)
+static EncodeTiledFn get_encode()
+{
+    std::call_once(g_encode_once, [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && fn && q == cudaDriverEntryPointSuccess)
+            g_encode = (EncodeTiledFn)fn;
+    });
+    return g_encode;
+}
 
 // 2-D fp32 tensor [rows][pitch] with a (box_rows x box_cols) tile
 static dwls_status make_tmap(dwls_ctx* ctx, CUtensorMap* tm, const float* base, int pitch, int64_t rows, int box_cols, int box_rows)
 {
-    if (!g_encode) {
-        void* fn = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
-        if (!fn || q != cudaDriverEntryPointSuccess) return fail(ctx, DWLS_CUDA_ERROR, "cuTensorMapEncodeTiled is not available in this driver");
-        g_encode = (EncodeTiledFn)fn;
-    }
+    if (!get_encode()) return fail(ctx, DWLS_CUDA_ERROR, "cuTensorMapEncodeTiled is not available in this driver");
     const cuuint64_t dims[2] = { (cuuint64_t)pitch, (cuuint64_t)rows };
     const cuuint64_t strides[1] = { (cuuint64_t)pitch * sizeof(float) };
     const cuuint32_t box[2] = { (cuuint32_t)box_cols, (cuuint32_t)box_rows };
@@ -500,12 +525,7 @@ static bool make_tmap_s16(dwls_ctx* ctx, CUtensorMap* tm, const int16_t* base, i
 {
     if (((uintptr_t)base & 15) || (step_elems & 7) || step_elems <= 0) return false;
     if (frames > 1 && ((frame_elems & 7) || frame_elems <= 0)) return false;
-    if (!g_encode) {
-        void* fn = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn || q != cudaDriverEntryPointSuccess) return false;
-        g_encode = (EncodeTiledFn)fn;
-    }
+    if (!get_encode()) return false;
     const cuuint64_t dims[3] = { (cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)frames };
     const cuuint64_t strides[2] = { (cuuint64_t)step_elems * 2, (cuuint64_t)(frames > 1 ? frame_elems : step_elems * rows) * 2 };
     const cuuint32_t box[3] = { 256, (cuuint32_t)box_rows, 1 };
@@ -835,11 +855,13 @@ extern "C" dwls_status dwls_filter_batch_dev(dwls_ctx* ctx, const dwls_batch* b,
     const WsLayout L = ws_layout(g, p->use_confidence != 0);
     const int G = pick_group(ctx, L.per_frame * sizeof(float), b->n_frames);
     if ((s = ensure(ctx, &ctx->ws, &ctx->ws_bytes, align256((size_t)G * L.per_frame * sizeof(float))))) return s;
+    CK(call_enter(ctx, st));
     if ((s = ensure_lut(ctx, (float)p->sigma_color, st))) return s;
     for (int f0 = 0; f0 < b->n_frames; f0 += G) {
         const int nf = (b->n_frames - f0 < G) ? b->n_frames - f0 : G;
         if ((s = filter_frames_graphed(ctx, b, f0, nf, g, p, roi_in, st))) return s;
     }
+    CK(call_leave(ctx, st));
     return DWLS_OK;
 }
 
@@ -1004,6 +1026,7 @@ static dwls_status filter_host_impl(dwls_ctx* ctx, const dwls_image* dl, const d
     if (s) return s;
     CK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
+    CK(call_enter(ctx, st));
     const bool want_conf = !mask_only && useconf && conf && conf->data;
     const size_t b_dl = align256((size_t)dw * dh * 2), b_view = mask_only ? 0 : align256((size_t)W * H * vcn),
                  b_out = mask_only ? 0 : align256((size_t)W * H * 2), b_conf = want_conf ? align256((size_t)W * H * 4) : 0,
@@ -1167,7 +1190,11 @@ extern "C" dwls_status dwls_fgs_dev(dwls_ctx* ctx, const dwls_image* guide, cons
     dwls_status s = fgs_check(ctx, guide, src, dst, lambda, sigma, num_iter);
     if (s) return s;
     CK(cudaSetDevice(ctx->device));
-    return fgs_dev_impl(ctx, guide, src, dst, lambda, sigma, att, num_iter, stream ? (cudaStream_t)stream : ctx->stream, nullptr, nullptr);
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    CK(call_enter(ctx, st));
+    if ((s = fgs_dev_impl(ctx, guide, src, dst, lambda, sigma, att, num_iter, st, nullptr, nullptr))) return s;
+    CK(call_leave(ctx, st));
+    return DWLS_OK;
 }
 
 extern "C" dwls_status dwls_fgs_host(dwls_ctx* ctx, const dwls_image* guide, const dwls_image* src, dwls_image* dst, double lambda,
@@ -1178,6 +1205,7 @@ extern "C" dwls_status dwls_fgs_host(dwls_ctx* ctx, const dwls_image* guide, con
     if (s) return s;
     CK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
+    CK(call_enter(ctx, st));
     const int w = guide->cols, h = guide->rows;
     const size_t grow = (size_t)w * guide->channels, srow = (size_t)w * src->channels * elem_size(src->depth);
     const size_t b_g = align256(grow * h), b_s = align256(srow * h);
@@ -1202,6 +1230,7 @@ extern "C" dwls_status dwls_fgs_weights_host(dwls_ctx* ctx, const dwls_image* gu
         return fail(ctx, DWLS_BAD_ARG, "guide must be non-empty CV_8UC1 / CV_8UC3, sigma_color >= 0");
     CK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
+    CK(call_enter(ctx, st));
     const int w = guide->cols, h = guide->rows;
     const size_t grow = (size_t)w * guide->channels, b_g = align256(grow * h), b_w = align256((size_t)w * h * 4);
     dwls_status s;
@@ -1275,6 +1304,8 @@ extern "C" dwls_status dwls_filter_batch_host(dwls_ctx* ctx, const dwls_batch* h
     if (s) return s;
     CK(cudaSetDevice(ctx->device));
     if (!ctx->stream2) CK(cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+    CK(call_enter(ctx, ctx->stream));
+    CK(call_enter(ctx, ctx->stream2));
     const bool useconf = p->use_confidence != 0, want_conf = useconf && hb->conf;
     const int dw = g.dw, dh = g.dh, W = g.W, H = g.H, vcn = g.vcn;
     const WsLayout L = ws_layout(g, useconf);
@@ -1333,5 +1364,6 @@ extern "C" dwls_status dwls_filter_batch_host(dwls_ctx* ctx, const dwls_batch* h
     }
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream2));
+    ctx->busy_valid = false;                 // nothing of this ctx is in flight any more
     return DWLS_OK;
 }

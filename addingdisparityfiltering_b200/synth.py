@@ -62,3 +62,47 @@ def make_textured_scene(w, h, channels=3, seed=42, max_disp=160, n_rect=8):
     if channels == 1:
         view = view[:, :, 0]
     return view, left, right
+
+
+def _gauss_blur(a, sigma):
+    """Separable Gaussian blur (reflect borders), numpy only."""
+    r = max(1, int(3 * sigma + 0.5))
+    k = np.exp(-0.5 * (np.arange(-r, r + 1) / sigma) ** 2)
+    k /= k.sum()
+    for axis in (0, 1):
+        pad = [(0, 0)] * a.ndim
+        pad[axis] = (r, r)
+        p = np.pad(a, pad, mode="reflect")
+        acc = np.zeros_like(a)
+        for i, kv in enumerate(k):
+            sl = [slice(None)] * a.ndim
+            sl[axis] = slice(i, i + a.shape[axis])
+            acc += kv * p[tuple(sl)]
+        a = acc
+    return a
+
+
+def make_stereo_pair(w, h, seed=42, n_rect=8, bg_disp=16, min_disp=24, max_disp=140):
+    """Generator G2: a rectified colour stereo pair for REAL matchers (cv2.StereoBM / StereoSGBM).
+    Left view = 3-channel uniform noise blurred with sigma 1.5 px plus n_rect rectangles of distinct mean colour;
+    true disparity = bg_disp px background, rectangles at U[min_disp, max_disp] px; right view by forward warping the
+    left one (nearer surfaces win, holes keep an independent noise texture).  Returns (left, right, true_disparity_px)."""
+    rng = np.random.default_rng(seed)
+    left = _gauss_blur(rng.integers(0, 256, (h, w, 3)).astype(np.float32), 1.5)
+    left = 128 + (left - 128) * 2.5                                       # the blur flattens the contrast: stretch it back
+    disp = np.full((h, w), bg_disp, np.int32)
+    for _ in range(n_rect):
+        rw, rh = int(rng.integers(w // 16, w // 3)), int(rng.integers(h // 16, h // 3))
+        x, y = int(rng.integers(0, w - rw)), int(rng.integers(0, h - rh))
+        disp[y:y + rh, x:x + rw] = int(rng.integers(min_disp, max_disp + 1))
+        left[y:y + rh, x:x + rw] = 0.5 * left[y:y + rh, x:x + rw] + rng.integers(0, 128, 3)
+    left = np.clip(np.rint(left), 0, 255).astype(np.uint8)
+    hole = _gauss_blur(rng.integers(0, 256, (h, w, 3)).astype(np.float32), 1.5)
+    right = np.clip(np.rint(128 + (hole - 128) * 2.5), 0, 255).astype(np.uint8)
+    ys = np.repeat(np.arange(h)[:, None], w, 1)
+    for d in np.unique(disp):                                            # increasing disparity: nearer surfaces overwrite
+        m = disp == d
+        xs = np.arange(w)[None, :] - d
+        ok = m & (xs >= 0)
+        right[ys[ok], np.broadcast_to(xs, (h, w))[ok]] = left[ok]
+    return left, right, disp

@@ -3,13 +3,21 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--frames B]
 
-One "step" = one pass of the hot path (confidence + LRC + weights + 6 FGS sweeps + normalise) over
-a batch of B independent synthetic 1080p stereo frames (BASELINE.json configs[1]: 1920x1080,
-SGBM-style geometry: ROI (160,0,1760,1080), discontinuity radius 2, LRC threshold 24, lambda 8000,
-sigma 1.5, 3-channel guide).  `value` times the device-resident path (inputs already in HBM, batch
-larger than L2); `e2e` times the same batch through the host-buffer C-ABI call with pinned host
-memory, H2D and D2H copies inside the timed region.  N > 1: one process per GPU (torchrun), every
-rank filters its own B frames, no collective on the data path ("weak" scaling); time = max over ranks.
+One "step" = one pass of the hot path (confidence + LRC + weights + 6 FGS sweeps + normalise) over a batch of B = 512
+independent 1080p stereo frames (BASELINE.json configs[4]; every frame has the configs[1] shape the metric is quoted on:
+1920x1080, cv2.StereoSGBM(0,160,3) left + right disparities of a synthetic stereo pair, ROI (160,0,1760,1080),
+discontinuity radius 2, LRC threshold 24, lambda 8000, sigma 1.5, 3-channel guide), resident in HBM.
+
+N > 1 (torchrun, one process per GPU): the SAME 512 frames are sharded in contiguous blocks over the ranks
+("strong" scaling; frames are independent, disparity_filters.cpp:138-139), each rank filters its block chunk by chunk and
+the CV_16S results are gathered to rank 0 over NCCL INSIDE the timed region: the grouped send/recv of chunk k runs on
+NCCL's stream beside the kernels of chunk k+1 (batch.ShardedBatch).  `value` = compute + gather; `compute_only` is the
+same step without the gather.  Time = CUDA events, max over ranks.
+
+`e2e` times the host-buffer C-ABI call (dwls_filter_batch_host: pinned host memory, H2D and D2H copies inside the timed
+region) with and without the confidence map copied back.  At N = 1 the line also carries `single_call` (one 1080p frame:
+device call and the cv::Mat-facade call on pageable memory) and `other_configs` (configs[2] FGS 3840x2160, configs[3]
+half-resolution 1080p).
 """
 import argparse
 import json
@@ -28,7 +36,9 @@ METRIC = "Mpix/s for 1080p DisparityWLSFilter::filter at 1/2/4/8 B200; achieved 
 W, H, CN = 1920, 1080, 3
 ROI = (160, 0, 1760, 1080)
 LAMBDA, SIGMA, RADIUS, LRC = 8000.0, 1.5, 2, 24
-WORKLOAD = "configs[1]: 1920x1080 SGBM-geometry disparities, confidence-aware WLS filter with LRC check"
+WORKLOAD = "configs[1] frames (1920x1080 StereoSGBM left+right disparities, confidence-aware WLS filter with LRC check) in the " \
+           "configs[4] batch of 512 frames sharded over the GPUs"
+N_BASE = 2
 
 
 def algorithmic_bytes(n_roi, f_disp, f_view, cn, S=2, P=6):
@@ -95,8 +105,26 @@ class ClockSampler:
 
 
 def make_base_frames(n_base):
+    """The distinct stereo frames every step is built from (frame f of the batch = base frame f % n_base shifted
+    horizontally).  Generator G2 of SURVEY section 8d: a synthetic colour stereo pair matched by the REAL
+    cv2.StereoSGBM configured exactly as createDisparityWLSFilter / createRightMatcher configure it
+    (disparity_filters.cpp:404-408, 430-441; sample lines 162-175).  Returns ([(view, disp_left, disp_right)], source)."""
     from addingdisparityfiltering_b200 import synth
-    return [synth.make_textured_scene(W, H, CN, seed=42 + i, max_disp=160) for i in range(n_base)]
+    try:
+        import cv2
+        import addingdisparityfiltering_b200 as A
+        frames = []
+        for i in range(n_base):
+            left, right, _ = synth.make_stereo_pair(W, H, seed=42 + i)
+            lm = cv2.StereoSGBM_create(0, 160, 3)
+            lm.setP1(24 * 9); lm.setP2(96 * 9); lm.setPreFilterCap(63); lm.setMode(cv2.STEREO_SGBM_MODE_SGBM_3WAY)
+            f = A.createDisparityWLSFilter(lm)                   # host-only: mutates the matcher, derives the margins
+            assert f._offsets == (ROI[0], 0, 0, 0) and f.getDepthDiscontinuityRadius() == RADIUS
+            rm = A.createRightMatcher(lm)
+            frames.append((left, lm.compute(left, right), rm.compute(right, left)))
+        return frames, "cv2.StereoSGBM(0,160,3,P1=216,P2=864,cap 63,3WAY) on synth.make_stereo_pair (G2)"
+    except ImportError:
+        return [synth.make_textured_scene(W, H, CN, seed=42 + i, max_disp=160) for i in range(n_base)], "synth.make_textured_scene (cv2 not importable)"
 
 
 def cpu_kind():
@@ -125,13 +153,31 @@ def cpu_frames_per_sec(base, n_frames, threads):
     return n_frames / (time.perf_counter() - t0)
 
 
+def default_chunk(world):
+    return 32 if world == 1 else 16
+
+
+def base_config(frames_total, world, source, chunk=0):
+    """`config` is the same dict in the GPU arm and in the reference arm (the driver compares them); what is specific to a
+    GPU run (shards, chunk plan, gather) goes into the line's `run` block."""
+    chunk = chunk or default_chunk(world)
+    return {"workload": WORKLOAD, "frames_total": frames_total, "roi": list(ROI), "lambda": LAMBDA, "sigma_color": SIGMA,
+            "disc_radius": RADIUS, "lrc_thresh": LRC, "guide_channels": CN, "confidence_export": True, "inputs": source,
+            "l2": "inputs larger than L2: a launch chunk's working set (%.0f MB inputs+outputs for %d frames) exceeds the 126 MB L2, "
+                  "no flush between iterations" % (chunk * (2 * 2 * W * H + CN * W * H + 6 * W * H) / 1e6, chunk)}
+
+
+CPU_NOTE = "kind=reference: the reference's fgs_filter.cpp + disparity_filters.cpp compiled unmodified (-O3, SSE2 universal intrinsics, " \
+           "parallel_for_ over all host threads) against the in-repo OpenCV-core stand-in; boxFilter/resize are the stand-in's"
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle import oracle as O
     threads = O.hardware_threads()
-    base = make_base_frames(2)
+    base, source = make_base_frames(N_BASE)
     S = args.ref_frames
     for _ in range(args.warmup):
         cpu_frames_per_sec(base, S, threads)
@@ -140,68 +186,171 @@ def run_reference(args):
         cpu_frames_per_sec(base, S, threads)
     dt = time.perf_counter() - t0
     v = args.steps * S * W * H / dt / 1e6
-    sample = "%d frames per step of the same 1080p workload, %d steps" % (S, args.steps)
+    sample = "%d frames per step of the same 1080p workload (a bounded sample of the %d-frame batch), %d steps" % (S, args.frames, args.steps)
+    cfg = base_config(args.frames, args.gpus, source)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "Mpix/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic", "config": {"workload": WORKLOAD, "frames_per_step": S, "roi": list(ROI), "lambda": LAMBDA, "sigma_color": SIGMA},
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": cfg,
         "cpu_baseline": {"value": v, "unit": "Mpix/s", "cores": threads, "kind": cpu_kind(), "sample": sample},
         "e2e": {"value": v, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
-        "note": "kind=reference: the reference's fgs_filter.cpp + disparity_filters.cpp compiled unmodified (SSE2 universal intrinsics, "
-                "parallel_for_ over all host threads) against the in-repo OpenCV-core stand-in; boxFilter/resize are the stand-in's"}))
+        "gpu_launches": 0, "note": CPU_NOTE}))
+
+
+def cuda_time(torch, fn, reps, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def extras_single_gpu(torch, A, ctx, dev, base, peak):
+    """N = 1 only: single-call latency (device and cv::Mat-facade path) and the other BASELINE configs, each device-timed."""
+    import ctypes as C
+    from addingdisparityfiltering_b200 import _lib, synth
+    from addingdisparityfiltering_b200.batch import BatchFilter
+    res = {}
+    view, dl, dr = base[0]
+    # ---- one 1080p frame per call ----
+    bf = BatchFilter(True, LAMBDA, SIGMA, LRC, RADIUS, ctx=ctx)
+    tv, tl, tr = (torch.from_numpy(a[None]).to(dev) for a in (view, dl, dr))
+    out = torch.empty((1, H, W), dtype=torch.int16, device=dev)
+    conf = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+    dev_us = cuda_time(torch, lambda: bf.filter_device(tl, tv, out, tr, conf, ROI), 50, 5) * 1e3
+    n_roi = ROI[2] * ROI[3]
+    alg, _ = algorithmic_bytes(n_roi, W * H, W * H, CN)
+    f = A.createDisparityWLSFilterGeneric(True, ctx=ctx)
+    f.setLambda(LAMBDA); f.setSigmaColor(SIGMA); f.setLRCthresh(LRC); f.setDepthDiscontinuityRadius(RADIUS)
+    for _ in range(3):
+        f.filter(dl, view, None, dr, ROI)
+    t0 = time.perf_counter()
+    for _ in range(20):
+        f.filter(dl, view, None, dr, ROI)
+    host_ms = (time.perf_counter() - t0) * 1e3 / 20
+    res["single_call"] = {"device_us": round(dev_us, 1), "device_Mpix_per_s": round(W * H / dev_us, 1), "device_alg_roofline_frac": round(alg / (dev_us * 1e-6) / 1e9 / peak, 3),
+                          "facade_pageable_ms": round(host_ms, 3), "facade_Mpix_per_s": round(W * H / host_ms / 1e3, 1),
+                          "what": "one 1080p frame per call: dwls_filter_batch_dev with n_frames=1 on device buffers (graph replay), and "
+                                  "dwls_filter_host on pageable numpy arrays incl. the confidence map (what wls->filter(cv::Mat...) calls)"}
+    other = {}
+    # ---- configs[3]: half resolution, 32 frames ----
+    try:
+        import cv2
+        B = 32
+        dl2 = (cv2.resize(dl, None, fx=0.5, fy=0.5) // 2).astype(np.int16)
+        dr2 = (cv2.resize(dr, None, fx=0.5, fy=0.5) // 2).astype(np.int16)
+        hv = torch.from_numpy(view).to(dev).expand(B, -1, -1, -1).contiguous()
+        hl = torch.from_numpy(dl2).to(dev).expand(B, -1, -1).contiguous()
+        hr = torch.from_numpy(dr2).to(dev).expand(B, -1, -1).contiguous()
+        o2 = torch.empty((B, H, W), dtype=torch.int16, device=dev)
+        c2 = torch.empty((B, H, W), dtype=torch.float32, device=dev)
+        bf2 = BatchFilter(True, LAMBDA, SIGMA, 24, 3, ctx=ctx)
+        roi2 = (83, 3, 874, 534)
+        ms = cuda_time(torch, lambda: bf2.filter_device(hl, hv, o2, hr, c2, roi2), 5, 2)
+        N, n, fd = 1748 * 1068, 874 * 534, 960 * 540
+        alg4 = 14 * n + 4 * fd + 6 * fd + 6 * W * H + 14 * N + (CN + 8) * N + 6 * (4 * N + 16 * N) - 8 * N + 2 * W * H
+        other["configs[3] half-res 1080p (960x540 maps, ROI (83,3,874,534), r=3), 32 frames"] = {
+            "Mpix_per_s": round(B * W * H / ms / 1e3, 1), "us_per_frame": round(ms * 1e3 / B, 2), "alg_roofline_frac": round(alg4 * B / (ms * 1e-3) / 1e9 / peak, 3)}
+        del hv, hl, hr, o2, c2
+    except ImportError:
+        pass
+    # ---- configs[2]: fastGlobalSmootherFilter 3840x2160, 3-channel guide ----
+    W4, H4 = 3840, 2160
+    rng = np.random.default_rng(7)
+    g = synth._gauss_blur(rng.integers(0, 256, (H4, W4, 3)).astype(np.float32), 2.0)
+    g = np.clip(np.rint(128 + (g - 128) * 3.0), 0, 255).astype(np.uint8)
+    lib = _lib.lib()
+    lib.dwls_fgs_dev.argtypes = [C.c_void_p, C.POINTER(_lib.Image), C.POINTER(_lib.Image), C.POINTER(_lib.Image), C.c_double, C.c_double, C.c_double, C.c_int, C.c_void_p]
+
+    def img(t, depth, cn):
+        return _lib.Image(t.data_ptr(), t.stride(0) * t.element_size(), t.shape[0], t.shape[1], depth, cn)
+    tg = torch.from_numpy(g).to(dev)
+    N4 = W4 * H4
+    for name, src, depth, cn, b in (("32FC1", torch.rand((H4, W4), device=dev) * 255, 5, 1, 4), ("8UC3", tg.clone(), 0, 3, 1)):
+        dst = torch.empty_like(src)
+        G_, S_, D_ = img(tg, 0, 3), img(src, depth, cn), img(dst, depth, cn)
+        stream = torch.cuda.current_stream().cuda_stream or 1
+
+        def run():
+            st = lib.dwls_fgs_dev(ctx.handle, C.byref(G_), C.byref(S_), C.byref(D_), 1000.0, 10.0, 0.25, 3, C.c_void_p(stream))
+            assert st == 0, st
+        ms = cuda_time(torch, run, 10, 3)
+        alg3 = (3 + 8) * N4 + 6 * (4 * N4 + 8 * cn * N4) - 2 * (4 - b) * cn * N4
+        other["configs[2] fastGlobalSmootherFilter 3840x2160 guide 8UC3, src %s, one frame" % name] = {
+            "ms_per_call": round(ms, 4), "Mpix_per_s": round(N4 / ms / 1e3, 1), "alg_roofline_frac": round(alg3 / (ms * 1e-3) / 1e9 / peak, 3)}
+    res["other_configs"] = other
+    return res
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--frames", type=int, default=32, help="frames per step per GPU")
-    ap.add_argument("--group", type=int, default=0, help="frames per kernel launch group (0 = library default)")
+    ap.add_argument("--frames", type=int, default=512, help="frames of the whole batch per step (sharded over the GPUs)")
+    ap.add_argument("--chunk", type=int, default=0, help="frames per launch / gather chunk (0 = 32 on one GPU, 16 on several)")
+    ap.add_argument("--tail-min", type=int, default=-1, help="smallest halved tail chunk (-1 = 0 on one GPU, 4 on several)")
+    ap.add_argument("--gather-mode", default="root", choices=["root", "all"])
+    ap.add_argument("--group", type=int, default=0, help="frames per kernel launch group inside a chunk (0 = library default)")
+    ap.add_argument("--e2e-frames", type=int, default=64, help="frames per rank and step of the end-to-end (host buffer) leg")
     ap.add_argument("--ref-frames", type=int, default=4)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--interleave", action="store_true", help="A/B switch: sector-interleaved solver planes (dwls_set_plane_interleave)")
-    ap.add_argument("--gather", action="store_true", help="all_gather the outputs over NCCL inside the timed region")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (tuning runs only)")
+    ap.add_argument("--no-extras", action="store_true", help="skip single_call / other_configs (tuning runs only)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
 
     import torch
     import addingdisparityfiltering_b200 as A
-    from addingdisparityfiltering_b200.batch import BatchFilter, gather_results
+    from addingdisparityfiltering_b200.batch import BatchFilter, ShardedBatch
 
     rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
     dist = None
-    if world > 1:
-        import torch.distributed as dist
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
     ctx = A.Context(local)
     if args.group:
         ctx.set_group_frames(args.group)
     if args.interleave:
         ctx.set_plane_interleave(True)
-    B = args.frames
+    chunk = args.chunk or default_chunk(world)
+    tail_min = args.tail_min if args.tail_min >= 0 else (0 if world == 1 else 4)
 
-    base = make_base_frames(2)
-    tb = [[torch.from_numpy(a).to(dev) for a in fr] for fr in base]
-    view = torch.stack([torch.roll(tb[(f + rank) % 2][0], shifts=3 * f + rank, dims=1) for f in range(B)]).contiguous()
-    dl = torch.stack([torch.roll(tb[(f + rank) % 2][1], shifts=3 * f + rank, dims=1) for f in range(B)]).contiguous()
-    dr = torch.stack([torch.roll(tb[(f + rank) % 2][2], shifts=3 * f + rank, dims=1) for f in range(B)]).contiguous()
-    out = torch.empty((B, H, W), dtype=torch.int16, device=dev)
-    conf = torch.empty((B, H, W), dtype=torch.float32, device=dev)
+    # ---- inputs: rank 0 runs the stereo matcher, the other ranks receive the base frames over NCCL ----
+    if rank == 0:
+        base, source = make_base_frames(N_BASE)
+        tb = [[torch.from_numpy(a).to(dev) for a in fr] for fr in base]
+    else:
+        base, source = None, None
+        tb = [[torch.empty((H, W, CN), dtype=torch.uint8, device=dev), torch.empty((H, W), dtype=torch.int16, device=dev),
+               torch.empty((H, W), dtype=torch.int16, device=dev)] for _ in range(N_BASE)]
+    if dist is not None:
+        for fr in tb:
+            for t in fr:
+                dist.broadcast(t.view(torch.uint8), src=0)
+    sb = ShardedBatch(args.frames, (H, W), chunk=chunk, tail_min=tail_min, mode=args.gather_mode, dst=0, device=dev)
+    nloc = sb.end - sb.begin
+
+    def build(k):          # frame f of the batch = base frame f % N_BASE rolled by 3 f columns (left / right / view alike)
+        return torch.stack([torch.roll(tb[f % N_BASE][k], shifts=3 * f, dims=1) for f in range(sb.begin, sb.end)]).contiguous()
+    view, dl, dr = build(0), build(1), build(2)
+    conf = torch.empty((nloc, H, W), dtype=torch.float32, device=dev)
     bf = BatchFilter(True, LAMBDA, SIGMA, LRC, RADIUS, ctx=ctx)
 
-    def step():
-        bf.filter_device(dl, view, out, dr, conf, ROI)
-        if args.gather and world > 1:
-            gather_results(out)
+    def filt(f0, nf, out):
+        bf.filter_device(dl[f0:f0 + nf], view[f0:f0 + nf], out, dr[f0:f0 + nf], conf[f0:f0 + nf], ROI)
 
     def sync_all():
         torch.cuda.synchronize()
@@ -209,68 +358,90 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def timed(steps, gather):
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            sb.run(filt, gather=gather)
+        e1.record()
+        sync_all()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
     for _ in range(args.warmup):
-        step()
+        sb.run(filt, gather=True)
     sync_all()
     sampler = ClockSampler(local) if rank == 0 else None
     time.sleep(0.15 if rank == 0 else 0.0)
-    sync_all()
     lo = sampler.mark() if sampler else 0
     launches0 = ctx.kernel_launches()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        step()
-    e1.record()
-    sync_all()
-    ms = e0.elapsed_time(e1)
+    sent0 = sb.bytes_sent
+    ms = timed(args.steps, True)                                   # THE timed region: compute + gather
     launches = ctx.kernel_launches() - launches0
+    sent = torch.tensor([float(sb.bytes_sent - sent0)], device=dev)
+    if dist is not None:
+        dist.all_reduce(sent)
+    ms_compute = timed(args.steps, False) if world > 1 else ms     # same step without the collective
     # per-kernel durations: the same K steps again with a CUDA-event bracket around every launch (on the launching
-    # stream).  The brackets cost about 3 % of the step, so they stay out of the pass `value` is taken from.
+    # stream).  The brackets cost a few % of the step, so they stay out of the pass `value` is taken from.
     ctx.kernel_timing_report()
     ctx.set_kernel_timing(True)
-    b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    b0.record()
-    for _ in range(args.steps):
-        step()
-    b1.record()
-    sync_all()
+    ms_bracketed = timed(args.steps, False)
     hi = sampler.mark() if sampler else 0
-    ms_bracketed = b0.elapsed_time(b1)
     ktimes = ctx.kernel_timing_report()
     ctx.set_kernel_timing(False)
-    if dist is not None:
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
     clocks = sampler.stop(lo, hi + 1) if sampler else None
-    value = world * B * args.steps * W * H / (ms * 1e-3) / 1e6
+    value = args.frames * args.steps * W * H / (ms * 1e-3) / 1e6
+    # gathered batch: spot-check on the root that what arrived is what a rank computed (frame 0 of the last rank's shard)
+    if world > 1:
+        probe = sb.local[0].clone() if rank == world - 1 else torch.empty((H, W), dtype=torch.int16, device=dev)
+        dist.broadcast(probe.view(torch.uint8), src=world - 1)
+        if rank == 0:
+            assert torch.equal(sb.full[sb.spans[world - 1][0]], probe), "gathered frame differs from the frame its rank computed"
+    zero_conf = float((conf[0, ROI[1]:ROI[1] + ROI[3], ROI[0]:ROI[0] + ROI[2]] == 0).float().mean().item())
 
-    # ---- end to end through the host-buffer entry point (pinned memory) ----
+    # ---- end to end through the host-buffer entry point (pinned memory), with and without the confidence map ----
     e2e = None
     if not args.no_e2e:
-        hv, hl, hr = view.cpu().pin_memory(), dl.cpu().pin_memory(), dr.cpu().pin_memory()
+        B = min(args.e2e_frames, nloc)
+        hv, hl, hr = view[:B].cpu().pin_memory(), dl[:B].cpu().pin_memory(), dr[:B].cpu().pin_memory()
         ho = torch.empty((B, H, W), dtype=torch.int16).pin_memory()
-        for _ in range(2):
-            bf.filter_host(hl, hv, ho, hr, None, ROI)
-        sync_all()
-        x0 = ctx.transfer_bytes()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            bf.filter_host(hl, hv, ho, hr, None, ROI)
-        torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        x1 = ctx.transfer_bytes()
-        assert torch.equal(ho.to(dev), out), "host-path result differs from the device-path result"
-        if dist is not None:
-            t = torch.tensor([dt], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dt = float(t.item())
-        e2e = {"value": world * B * args.steps * W * H / dt / 1e6, "unit": "Mpix/s",
-               "h2d_bytes_per_step": (x1[0] - x0[0]) // args.steps, "d2h_bytes_per_step": (x1[1] - x0[1]) // args.steps,
+        hc = torch.empty((B, H, W), dtype=torch.float32).pin_memory()
+        esteps = max(2, min(args.steps, 5))
+
+        def e2e_leg(hconf):
+            for _ in range(2):
+                bf.filter_host(hl, hv, ho, hr, hconf, ROI)
+            sync_all()
+            x0 = ctx.transfer_bytes()
+            t0 = time.perf_counter()
+            for _ in range(esteps):
+                bf.filter_host(hl, hv, ho, hr, hconf, ROI)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            x1 = ctx.transfer_bytes()
+            if dist is not None:
+                t = torch.tensor([dt], device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                dt = float(t.item())
+            return world * B * esteps * W * H / dt / 1e6, (x1[0] - x0[0]) // esteps, (x1[1] - x0[1]) // esteps
+        v0, h2d0, d2h0 = e2e_leg(None)
+        assert torch.equal(ho.to(dev), sb.local[:B]), "host-path result differs from the device-path result"
+        v1, h2d1, d2h1 = e2e_leg(hc)
+        assert torch.equal(hc.to(dev), conf[:B]), "host-path confidence map differs from the device-path one"
+        e2e = {"value": v0, "unit": "Mpix/s", "h2d_bytes_per_step": h2d0, "d2h_bytes_per_step": d2h0,
+               "with_confidence_map": {"value": v1, "unit": "Mpix/s", "h2d_bytes_per_step": h2d1, "d2h_bytes_per_step": d2h1},
+               "frames_per_rank_per_step": B, "steps": esteps,
                "host_input_bytes_per_step": int(hv.numel() + 2 * hl.numel() + 2 * hr.numel()),
                "api": "dwls_filter_batch_host (pinned host buffers, 2-lane copy/compute pipeline; uploads the ROI windows the filter "
-                      "reads, bytes counted by the library from the copies it issues)"}
+                      "reads, bytes counted by the library from the copies it issues); `value` returns the CV_16S maps only, "
+                      "`with_confidence_map` also copies back what getConfidenceMap() holds"}
+        del hv, hl, hr, ho, hc
 
     if rank != 0:
         if dist is not None:
@@ -281,27 +452,30 @@ def main():
     peak, peak_src = measured_peak_gbs()
     dom = max(ktimes.items(), key=lambda kv: kv[1][1])
     dom_name, (dom_n, dom_ms) = dom
-    frames_per_launch = B * args.steps * {"hsolve_kernel": 3, "vsolve_kernel": 2}.get(dom_name, 1) / dom_n
+    frames_per_launch = nloc * args.steps * {"hsolve_kernel": 3, "vsolve_kernel": 2}.get(dom_name, 1) / dom_n
     achieved = per_alg.get(dom_name, 0) * frames_per_launch / (dom_ms / dom_n * 1e-3) / 1e9
-    # DRAM bytes of the dominant kernel per launch from the committed ncu --set full capture (profiles/ncu_traffic_r01.json)
-    traffic = None
-    try:
-        tk = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic_r01.json")))["kernels"].get(dom_name)
-        if tk:
-            traffic = tk["dram_bytes_per_frame"] * frames_per_launch
-    except Exception:
-        pass
+    traffic = None           # DRAM bytes of the dominant kernel per launch from the committed ncu --set full capture
+    for prof in ("ncu_traffic_r02.json", "ncu_traffic_r01.json"):
+        try:
+            tk = json.load(open(os.path.join(ROOT, "profiles", prof)))["kernels"].get(dom_name)
+            if tk:
+                traffic = tk["dram_bytes_per_frame"] * frames_per_launch
+                break
+        except Exception:
+            pass
+    ksum = sum(v[1] for v in ktimes.values())
     roofline = {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": peak_src, "alg_bytes_per_launch": per_alg.get(dom_name, 0) * frames_per_launch,
                 "avg_launch_ms": dom_ms / dom_n,
-                "timing": "per-kernel CUDA events on the launching stream over a second pass of the same %d steps (%.4f ms/step with the "
-                          "brackets, %.4f without)" % (args.steps, ms_bracketed / args.steps, ms / args.steps),
-                "pipeline": {"alg_bytes_per_frame": total_alg, "achieved": total_alg * B * args.steps / (ms * 1e-3) / 1e9,
-                             "frac": total_alg * B * args.steps / (ms * 1e-3) / 1e9 / peak},
-                "kernels": {k: {"launches": n, "total_ms": round(t, 4), "share": round(t / sum(v[1] for v in ktimes.values()), 4)}
+                "timing": "per-kernel CUDA events on the launching stream over a further pass of the same %d steps without the gather "
+                          "(%.4f ms/step with the brackets, %.4f without)" % (args.steps, ms_bracketed / args.steps, ms_compute / args.steps),
+                "pipeline": {"alg_bytes_per_frame": total_alg, "achieved": total_alg * nloc * args.steps / (ms_compute * 1e-3) / 1e9,
+                             "frac": total_alg * nloc * args.steps / (ms_compute * 1e-3) / 1e9 / peak,
+                             "what": "whole step of this rank (all kernels, no gather): algorithmic bytes of its frames / its time"},
+                "kernels": {k: {"launches": n, "total_ms": round(t, 4), "share": round(t / ksum, 4),
+                                "frac": round(per_alg[k] * nloc * args.steps / (t * 1e-3) / 1e9 / peak, 3) if k in per_alg else None}
                             for k, (n, t) in ktimes.items()}}
-    # ---- CPU baseline: the oracle on a bounded sample, all host threads ----
-    cpu = None
+    cpu = None               # ---- CPU baseline: the reference's CPU code on a bounded sample, all host threads ----
     if not args.no_cpu:
         from oracle import oracle as O
         threads = O.hardware_threads()
@@ -309,15 +483,25 @@ def main():
         n_cpu = int(max(2, min(64, args.cpu_seconds * fps1)))
         fps = cpu_frames_per_sec(base, n_cpu, threads)
         cpu = {"value": fps * W * H / 1e6, "unit": "Mpix/s", "cores": threads, "kind": cpu_kind(),
-               "sample": "%d frames of the same 1080p workload, reference CPU code on all host threads" % n_cpu}
-    print(json.dumps({
+               "sample": "%d frames of the same 1080p workload, reference CPU code on all host threads" % n_cpu,
+               "zero_confidence_share_of_roi": round(zero_conf, 4), "note": CPU_NOTE}
+    cfg = base_config(args.frames, world, source, chunk)
+    run = {"frames_per_gpu": [e - b for b, e in sb.spans], "chunk_plan_rank0": [c for _, c in sb.plan],
+           "gather": "none (one rank holds the whole batch)" if world == 1 else
+                     "CV_16S results of every chunk sent to rank 0 with grouped ncclSend/ncclRecv on NCCL's stream while the next "
+                     "chunk's kernels run (mode %s)" % args.gather_mode,
+           "gather_in_timed_region": world > 1, "zero_confidence_share_of_roi": round(zero_conf, 4)}
+    line = {
         "metric": METRIC, "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "roi": list(ROI), "lambda": LAMBDA, "sigma_color": SIGMA,
-                   "disc_radius": RADIUS, "lrc_thresh": LRC, "guide_channels": CN, "confidence_export": True,
-                   "l2": "batch working set (%.0f MB inputs+outputs per step) larger than the 126 MB L2; no flush needed" % (B * (2 * 2 * W * H + CN * W * H + 6 * W * H) / 1e6),
-                   "gather_in_timed_region": bool(args.gather and world > 1)},
-        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks}))
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": cfg, "run": run, "gather_in_timed_region": world > 1,
+        "compute_only": {"value": args.frames * args.steps * W * H / (ms_compute * 1e-3) / 1e6, "unit": "Mpix/s", "ms_per_step": ms_compute / args.steps,
+                         "what": "the same step without the NCCL gather (separate timed pass)"},
+        "nvlink_bytes_per_step": int(sent.item()) // args.steps,
+        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks}
+    if world == 1 and not args.no_extras:
+        line.update(extras_single_gpu(torch, A, ctx, dev, base, peak))
+    print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
 

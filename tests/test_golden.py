@@ -71,3 +71,18 @@ def test_gpu_wls_against_reference_golden(ctx, i):
     assert_s16_parity(out, gold["out"], froi)                                       # <= 1 LSB on >= 99.9 %
     if conf:
         assert np.abs(f.getConfidenceMap() - gold["conf"]).max() <= 1e-4            # confidence within 1e-4
+
+
+def test_oracle_reproduces_reference_on_the_tutorial_pair_bit_exact():
+    """ambush_5 through the sample's default path (real cv2.StereoBM maps, half resolution, radius 3): the stored outputs
+    are the compiled reference's (tests/golden/make_golden_real.py)."""
+    pytest.importorskip("cv2")
+    from tests.stereo_inputs import ambush_fixture
+    z, left, _ = ambush_fixture()
+    if int(left.astype(np.int64).sum()) != int(z["left_sum"]):
+        pytest.skip("this cv2 build decodes the JPEG differently from the one that made the fixture")
+    r = O.wls_filter(z["dl"], left, z["dr"], lam=8000.0, sigma=1.5, disc_radius=int(z["radius"]), offsets=tuple(int(v) for v in z["offsets"]),
+                     assoc=1, nstripes=4)
+    assert r["rc"] == 0 and r["roi"] == tuple(int(v) for v in z["roi"])
+    assert (r["out"] == z["out"]).all() and (r["conf"] == z["conf"]).all()
+    assert (z["dl"] < 0).any()                      # a real matcher's invalid-disparity markers reach the LRC gather

@@ -189,3 +189,38 @@ def test_config5_batch_of_512_frames_1080p(ctx):
     ref = O.wls_filter(base[0][1], base[0][0], base[0][2], roi=roi, lam=8000.0, sigma=1.5, lrc_thresh=24, disc_radius=2)
     assert np.abs(conf[0].cpu().numpy() - ref["conf"]).max() <= 1e-4
     assert_s16_parity(out[0].cpu().numpy(), ref["out"], roi)
+
+
+def test_calls_on_different_streams_do_not_race_on_the_shared_workspace(ctx):
+    """Two asynchronous device calls on different torch streams share ctx workspace, LUT and graphs: the library orders
+    the second after the first (event recorded by each call), so both give the bytes of serialised runs even with
+    different sigma (the LUT is rewritten in place) and different batch sizes (other workspace layout)."""
+    import torch
+    dev = torch.device("cuda", 0)
+    w, h = 640, 480
+    roi = (80, 0, w - 80, h)
+    va, la, ra = _frames(12, w, h, 3, seed=300)
+    vb, lb, rb = _frames(5, w, h, 3, seed=400)
+    ta = [torch.from_numpy(x).to(dev) for x in (la, va, ra)]
+    tb = [torch.from_numpy(x).to(dev) for x in (lb, vb, rb)]
+    fa = BatchFilter(True, 8000.0, 1.5, 24, 2, ctx=ctx)
+    fb = BatchFilter(True, 500.0, 4.0, 24, 3, ctx=ctx)
+    want = []
+    for f, t in ((fa, ta), (fb, tb)):
+        o = torch.empty((t[0].shape[0], h, w), dtype=torch.int16, device=dev)
+        f.filter_device(t[0], t[1], o, t[2], None, roi)
+        torch.cuda.synchronize()
+        want.append(o.clone())
+    sa, sb = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    for rep in range(6):
+        oa = torch.full((12, h, w), 7, dtype=torch.int16, device=dev)
+        ob = torch.full((5, h, w), 7, dtype=torch.int16, device=dev)
+        torch.cuda.synchronize()
+        with torch.cuda.stream(sa):
+            fa.filter_device(ta[0], ta[1], oa, ta[2], None, roi)
+        with torch.cuda.stream(sb):
+            fb.filter_device(tb[0], tb[1], ob, tb[2], None, roi)       # no host sync in between
+        with torch.cuda.stream(sa):
+            fa.filter_device(ta[0], ta[1], oa, ta[2], None, roi)
+        torch.cuda.synchronize()
+        assert torch.equal(oa, want[0]) and torch.equal(ob, want[1]), rep

@@ -148,3 +148,33 @@ def test_two_rank_gather_on_gloo(tmp_path):
              for r in range(2)]
     outs = [p.communicate(timeout=180)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
+
+
+def test_batch_arguments_are_validated_before_reaching_the_c_abi():
+    """The batch path hands raw pointers and strides to the kernels: wrong dtype / shape / layout / placement must raise
+    BAD_ARG on the host (like image_of() does for single frames) instead of writing out of bounds on the device."""
+    import torch
+    from addingdisparityfiltering_b200 import DwlsError
+    from addingdisparityfiltering_b200.batch import _make_batch
+    n, h, w = 3, 8, 16
+    dl, v = np.zeros((n, h, w), np.int16), np.zeros((n, h, w, 3), np.uint8)
+    o, c = np.zeros((n, h, w), np.int16), np.zeros((n, h, w), np.float32)
+    b = _make_batch(dl, dl, v, o, c)
+    assert (b.n_frames, b.disp_cols, b.disp_rows, b.view_channels, b.dl_step, b.dl_frame, b.conf_step) == (n, w, h, 3, 2 * w, 2 * w * h, 4 * w)
+    big = np.zeros((n, h + 2, w + 4), np.int16)
+    b = _make_batch(big[:, 1:h + 1, 2:w + 2], None, torch.from_numpy(v)[..., 0].contiguous(), torch.from_numpy(o), None)   # row/frame-strided views are fine
+    assert (b.dl_step, b.dl_frame, b.view_channels) == (2 * (w + 4), 2 * (w + 4) * (h + 2), 1)
+    bad = [lambda: _make_batch(dl.astype(np.float32), dl, v, o, c),                 # CV_16S required (221)
+           lambda: _make_batch(dl, dl[:, :, :-1], v, o, c),                          # right map of another size (263)
+           lambda: _make_batch(dl, dl, v, o[:, :-1], c),                             # undersized output
+           lambda: _make_batch(dl, dl, v, o, c.astype(np.float64)),
+           lambda: _make_batch(dl[:, :, ::2], None, v[:, :, ::2], o[:, :, ::2], None),   # column-sliced view
+           lambda: _make_batch(np.transpose(dl, (0, 2, 1)), None, np.zeros((n, w, h), np.uint8), np.zeros((n, w, h), np.int16), None),
+           lambda: _make_batch(dl, dl, v, o, c, on_device=True),                     # host arrays handed to the device entry point
+           lambda: _make_batch(dl[:0], None, v[:0], o[:0], None),                    # empty batch
+           lambda: _make_batch(dl, None, v[..., 0], o, None),                        # channel-sliced guide
+           lambda: _make_batch(dl[::-1], None, v, o, None)]                          # negative frame stride
+    for f in bad:
+        with pytest.raises(DwlsError) as e:
+            f()
+        assert e.value.status == 1
