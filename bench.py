@@ -464,6 +464,7 @@ def main():
         except Exception:
             pass
     ksum = sum(v[1] for v in ktimes.values())
+    per_frame_launches = {"hsolve_kernel": 3, "vsolve_kernel": 2}
     roofline = {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": peak_src, "alg_bytes_per_launch": per_alg.get(dom_name, 0) * frames_per_launch,
                 "avg_launch_ms": dom_ms / dom_n,
@@ -473,7 +474,8 @@ def main():
                              "frac": total_alg * nloc * args.steps / (ms_compute * 1e-3) / 1e9 / peak,
                              "what": "whole step of this rank (all kernels, no gather): algorithmic bytes of its frames / its time"},
                 "kernels": {k: {"launches": n, "total_ms": round(t, 4), "share": round(t / ksum, 4),
-                                "frac": round(per_alg[k] * nloc * args.steps / (t * 1e-3) / 1e9 / peak, 3) if k in per_alg else None}
+                                "us_per_frame": round(t * 1e3 / (nloc * args.steps), 3),
+                                "frac": round(per_alg[k] * per_frame_launches.get(k, 1) * nloc * args.steps / (t * 1e-3) / 1e9 / peak, 3) if k in per_alg else None}
                             for k, (n, t) in ktimes.items()}}
     cpu = None               # ---- CPU baseline: the reference's CPU code on a bounded sample, all host threads ----
     if not args.no_cpu:
