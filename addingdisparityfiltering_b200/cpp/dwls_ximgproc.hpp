@@ -14,6 +14,7 @@
 #if defined(DWLS_USE_OPENCV) || (defined(__has_include) && __has_include(<opencv2/core.hpp>) && !defined(DWLS_USE_MINI_CV))
 #include <opencv2/calib3d.hpp>
 #include <opencv2/core.hpp>
+#include <opencv2/imgcodecs.hpp>
 #define DWLS_REAL_OPENCV 1
 #else
 #include "mini_cv.hpp"
@@ -21,6 +22,7 @@
 #endif
 
 #include <cmath>
+#include <cstdlib>
 #include <string>
 
 #include "../../include/dwls_b200.h"
@@ -237,6 +239,102 @@ inline void fastGlobalSmootherFilter(InputArray guide, InputArray src, OutputArr
                                      int num_iter = 3)
 {
     createFastGlobalSmootherFilter(guide, lambda, sigma_color, lambda_attenuation, num_iter)->filter(src, dst);
+}
+
+// ---- ground-truth / quality helpers of the sample (include/opencv2/ximgproc/disparity_filter.hpp:163-204,
+// src/disparity_filters.cpp:460-556): host-side like the reference's, a few integer operations per pixel ----
+namespace detail {
+enum { UNKNOWN_DISPARITY = 16320 };                                         // :460
+inline void check_s16_pair(const Mat& GT, const Mat& src, const Rect& ROI)
+{
+    if (GT.empty() || GT.depth() != CV_16S || GT.channels() != 1 || src.empty() || src.depth() != CV_16S || src.channels() != 1 ||
+        src.rows != GT.rows || src.cols != GT.cols)                         // CV_Assert (:499-501, :522-524)
+        throw Exception(Error::StsAssert, "GT and src must be non-empty CV_16SC1 images of equal size"
+#if DWLS_REAL_OPENCV
+                        , "dwls_b200", __FILE__, __LINE__
+#endif
+        );
+    if (ROI.x < 0 || ROI.y < 0 || ROI.width < 0 || ROI.height < 0 || ROI.x + ROI.width > GT.cols || ROI.y + ROI.height > GT.rows)
+        throw Exception(Error::StsAssert, "ROI outside the disparity map"   // Mat(m, roi) asserts
+#if DWLS_REAL_OPENCV
+                        , "dwls_b200", __FILE__, __LINE__
+#endif
+        );
+}
+}  // namespace detail
+
+// readGT (:462-495): Middlebury (1 channel: 0 = unknown, else 16 x value) and MPI-Sintel (3 channels: 64 R + G / 4) formats
+inline int readGT(String src_path, OutputArray dst_)
+{
+    const Mat src = imread(src_path, IMREAD_UNCHANGED);
+    detail::create_out(dst_, src.rows, src.cols, CV_16SC1);
+    Mat dst = detail::out_mat(dst_);
+    if (!src.empty() && src.channels() == 3 && src.depth() == CV_8U) {
+        for (int i = 0; i < src.rows; ++i) {
+            const unsigned char* s = src.ptr<unsigned char>(i);
+            short* d = dst.ptr<short>(i);
+            for (int j = 0; j < src.cols; ++j) d[j] = (short)(64 * s[3 * j + 2] + s[3 * j + 1] / 4);
+        }
+        return 0;
+    }
+    if (!src.empty() && src.channels() == 1 && src.depth() == CV_8U) {
+        for (int i = 0; i < src.rows; ++i) {
+            const unsigned char* s = src.ptr<unsigned char>(i);
+            short* d = dst.ptr<short>(i);
+            for (int j = 0; j < src.cols; ++j) d[j] = s[j] == 0 ? (short)detail::UNKNOWN_DISPARITY : (short)(16 * s[j]);
+        }
+        return 0;
+    }
+    return 1;
+}
+
+// computeMSE (:497-517): mean squared error over the known pixels of the ROI, in pixels^2 (disparities are stored x16)
+inline double computeMSE(InputArray GT_, InputArray src_, Rect ROI)
+{
+    const Mat GT = detail::mat_of(GT_), src = detail::mat_of(src_);
+    detail::check_s16_pair(GT, src, ROI);
+    double res = 0;
+    int cnt = 0;
+    for (int i = 0; i < ROI.height; ++i) {
+        const short* g = GT.ptr<short>(ROI.y + i) + ROI.x;
+        const short* s = src.ptr<short>(ROI.y + i) + ROI.x;
+        for (int j = 0; j < ROI.width; ++j)
+            if (g[j] != detail::UNKNOWN_DISPARITY) { res += (g[j] - s[j]) * (g[j] - s[j]); cnt++; }
+    }
+    return res / (cnt * 256);
+}
+
+// computeBadPixelPercent (:519-540)
+inline double computeBadPixelPercent(InputArray GT_, InputArray src_, Rect ROI, int thresh = 24 /*1.5 pixels*/)
+{
+    const Mat GT = detail::mat_of(GT_), src = detail::mat_of(src_);
+    detail::check_s16_pair(GT, src, ROI);
+    int bad = 0, cnt = 0;
+    for (int i = 0; i < ROI.height; ++i) {
+        const short* g = GT.ptr<short>(ROI.y + i) + ROI.x;
+        const short* s = src.ptr<short>(ROI.y + i) + ROI.x;
+        for (int j = 0; j < ROI.width; ++j)
+            if (g[j] != detail::UNKNOWN_DISPARITY) { if (std::abs(g[j] - s[j]) >= thresh) bad++; cnt++; }
+    }
+    return (100.0 * bad) / cnt;
+}
+
+// getDisparityVis (:542-556): saturate_cast<uchar>(scale * d / 16.0), unknown pixels black
+inline void getDisparityVis(InputArray src_, OutputArray dst_, double scale = 1.0)
+{
+    const Mat src = detail::mat_of(src_);
+    if (src.empty() || src.depth() != CV_16S || src.channels() != 1) detail::check(nullptr, DWLS_BAD_ARG);
+    detail::create_out(dst_, src.rows, src.cols, CV_8UC1);
+    Mat dst = detail::out_mat(dst_);
+    for (int i = 0; i < src.rows; ++i) {
+        const short* s = src.ptr<short>(i);
+        unsigned char* d = dst.ptr<unsigned char>(i);
+        for (int j = 0; j < src.cols; ++j) {
+            if (s[j] == detail::UNKNOWN_DISPARITY) { d[j] = 0; continue; }
+            const long r = std::lrint(scale * s[j] / 16.0);                 // cvRound: round half to even
+            d[j] = (unsigned char)(r < 0 ? 0 : r > 255 ? 255 : r);
+        }
+    }
 }
 
 }  // namespace DWLS_NAMESPACE

@@ -6,6 +6,7 @@
 #define DWLS_MINI_CV_HPP
 
 #include <cstdint>
+#include <cstdio>
 #include <cstring>
 #include <memory>
 #include <stdexcept>
@@ -79,6 +80,32 @@ public:
 private:
     std::shared_ptr<unsigned char> buf_;
 };
+
+// imread stand-in for readGT: binary netpbm only (P5 -> CV_8UC1, P6 -> CV_8UC3 in BGR order, like cv::imread(IMREAD_UNCHANGED)
+// of the same pixels).  With real OpenCV the facade calls cv::imread and reads whatever imgcodecs decodes.
+enum { IMREAD_UNCHANGED = -1 };
+inline Mat imread(const std::string& path, int = IMREAD_UNCHANGED)
+{
+    FILE* f = std::fopen(path.c_str(), "rb");
+    if (!f) return Mat();
+    char magic[3] = { 0, 0, 0 };
+    int w = 0, h = 0, maxv = 0;
+    if (std::fscanf(f, "%2s %d %d %d", magic, &w, &h, &maxv) != 4 || magic[0] != 'P' || (magic[1] != '5' && magic[1] != '6') || maxv != 255 || w <= 0 || h <= 0) {
+        std::fclose(f);
+        return Mat();
+    }
+    std::fgetc(f);
+    const int cn = magic[1] == '6' ? 3 : 1;
+    Mat m(h, w, CV_MAKETYPE(CV_8U, cn));
+    for (int i = 0; i < h; ++i) {
+        unsigned char* r = m.ptr<unsigned char>(i);
+        if (std::fread(r, 1, (size_t)w * cn, f) != (size_t)w * cn) { std::fclose(f); return Mat(); }
+        if (cn == 3) for (int j = 0; j < w; ++j) { const unsigned char t = r[3 * j]; r[3 * j] = r[3 * j + 2]; r[3 * j + 2] = t; }
+    }
+    std::fclose(f);
+    return m;
+}
+typedef std::string String;
 
 typedef const Mat& InputArray;
 typedef Mat& OutputArray;

@@ -71,3 +71,35 @@ def factory_geometry(kind, min_disp, num_disp, block, dw, dh):
     rc = lib().ref_factory_roi(0 if kind == "bm" else 1, min_disp, num_disp, block, dw, dh, roi, C.byref(rad), C.byref(rmin))
     assert rc == 0
     return tuple(roi), rad.value, rmin.value
+
+
+def read_gt(path, cap=1 << 24):
+    """readGT of the reference (disparity_filters.cpp:462-495) through the stand-in imread (binary PGM / PPM files)."""
+    dst = np.empty(cap, np.int16)
+    rows, cols = C.c_int(), C.c_int()
+    rc = lib().ref_read_gt(path.encode(), _p(dst), int(cap), C.byref(rows), C.byref(cols))
+    return rc, (dst[:rows.value * cols.value].reshape(rows.value, cols.value).copy() if rc == 0 else None)
+
+
+def compute_mse(gt, src, roi):
+    gt, src = np.ascontiguousarray(gt, np.int16), np.ascontiguousarray(src, np.int16)
+    out = C.c_double()
+    rc = lib().ref_compute_mse(_p(gt), _p(src), gt.shape[1], gt.shape[0], (C.c_int * 4)(*[int(v) for v in roi]), C.byref(out))
+    assert rc == 0
+    return out.value
+
+
+def bad_pixel_percent(gt, src, roi, thresh=24):
+    gt, src = np.ascontiguousarray(gt, np.int16), np.ascontiguousarray(src, np.int16)
+    out = C.c_double()
+    rc = lib().ref_bad_pixel_percent(_p(gt), _p(src), gt.shape[1], gt.shape[0], (C.c_int * 4)(*[int(v) for v in roi]), int(thresh), C.byref(out))
+    assert rc == 0
+    return out.value
+
+
+def disparity_vis(src, scale=1.0):
+    src = np.ascontiguousarray(src, np.int16)
+    dst = np.empty(src.shape, np.uint8)
+    rc = lib().ref_disparity_vis(_p(src), src.shape[1], src.shape[0], C.c_double(scale), _p(dst))
+    assert rc == 0
+    return dst

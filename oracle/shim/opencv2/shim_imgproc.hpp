@@ -1,3 +1,4 @@
+#include <cstdio>
 // oracle/shim/opencv2/shim_imgproc.hpp — TEST INFRASTRUCTURE (see core.hpp): the imgproc / imgcodecs /
 // calib3d entry points the reference calls.  Rounding sequences as verified against cv2 (non-IPP
 // build path) in tests/test_oracle_primitives.py.
@@ -82,7 +83,26 @@ inline void resize(InputArray _src, OutputArray _dst, Size dsize, double fx = 0,
     _dst.getMatRef() = out;
 }
 
-inline Mat imread(const String&, int = IMREAD_COLOR) { return Mat(); }     // readGT is outside the hot path; no codec here
+// imread stand-in for readGT (disparity_filters.cpp:462): binary netpbm only, P5 -> CV_8UC1, P6 -> CV_8UC3 in BGR order like
+// cv::imread(IMREAD_UNCHANGED) of the same pixels; anything else -> empty Mat (no PNG/JPEG codec on this box)
+inline Mat imread(const String& path, int = IMREAD_COLOR)
+{
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) return Mat();
+    char magic[3] = { 0, 0, 0 };
+    int w = 0, h = 0, maxv = 0;
+    if (fscanf(f, "%2s %d %d %d", magic, &w, &h, &maxv) != 4 || magic[0] != 'P' || (magic[1] != '5' && magic[1] != '6') || maxv != 255 || w <= 0 || h <= 0) { fclose(f); return Mat(); }
+    fgetc(f);
+    const int cn = magic[1] == '6' ? 3 : 1;
+    Mat m(h, w, CV_MAKETYPE(CV_8U, cn));
+    for (int i = 0; i < h; ++i) {
+        uchar* r = m.ptr<uchar>(i);
+        if (fread(r, 1, (size_t)w * cn, f) != (size_t)w * cn) { fclose(f); return Mat(); }
+        if (cn == 3) for (int j = 0; j < w; ++j) { const uchar t = r[3 * j]; r[3 * j] = r[3 * j + 2]; r[3 * j + 2] = t; }
+    }
+    fclose(f);
+    return m;
+}
 
 // ---- calib3d: the matcher interface createDisparityWLSFilter / createRightMatcher talk to ------
 class StereoMatcher : public Algorithm {

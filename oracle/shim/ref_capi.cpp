@@ -69,4 +69,42 @@ int ref_factory_roi(int kind, int min_disp, int num_disp, int block, int dw, int
     } catch (const cv::Exception&) { return 1; }
 }
 
+// quality / IO helpers of the sample (disparity_filters.cpp:460-556), the reference's own code
+int ref_read_gt(const char* path, short* dst, int cap, int* rows, int* cols)
+{
+    try {
+        Mat d;
+        const int rc = ximgproc::readGT(path, d);
+        *rows = d.rows; *cols = d.cols;
+        if (rc == 0 && (long long)d.rows * d.cols <= cap) { Mat o(d.rows, d.cols, CV_16SC1, dst, (size_t)d.cols * 2); d.copyTo(o); }
+        return rc;
+    } catch (const cv::Exception&) { return -1; }
+}
+int ref_compute_mse(const short* gt, const short* src, int w, int h, const int* roi, double* out)
+{
+    try {
+        Mat G(h, w, CV_16SC1, (void*)gt, (size_t)w * 2), S(h, w, CV_16SC1, (void*)src, (size_t)w * 2);
+        *out = ximgproc::computeMSE(G, S, Rect(roi[0], roi[1], roi[2], roi[3]));
+        return 0;
+    } catch (const cv::Exception&) { return 1; }
+}
+int ref_bad_pixel_percent(const short* gt, const short* src, int w, int h, const int* roi, int thresh, double* out)
+{
+    try {
+        Mat G(h, w, CV_16SC1, (void*)gt, (size_t)w * 2), S(h, w, CV_16SC1, (void*)src, (size_t)w * 2);
+        *out = ximgproc::computeBadPixelPercent(G, S, Rect(roi[0], roi[1], roi[2], roi[3]), thresh);
+        return 0;
+    } catch (const cv::Exception&) { return 1; }
+}
+int ref_disparity_vis(const short* src, int w, int h, double scale, unsigned char* dst)
+{
+    try {
+        Mat S(h, w, CV_16SC1, (void*)src, (size_t)w * 2), d;
+        ximgproc::getDisparityVis(S, d, scale);
+        Mat o(h, w, CV_8UC1, dst, (size_t)w);
+        d.copyTo(o);
+        return 0;
+    } catch (const cv::Exception&) { return 1; }
+}
+
 }  // extern "C"
