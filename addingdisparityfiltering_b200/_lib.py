@@ -49,7 +49,7 @@ class Batch(C.Structure):
 
 
 EXPORTS = ["dwls_default_params", "dwls_ctx_create", "dwls_ctx_destroy", "dwls_last_error", "dwls_version",
-           "dwls_kernel_launches", "dwls_set_group_frames", "dwls_set_kernel_timing", "dwls_kernel_timing_report", "dwls_set_cuda_graphs", "dwls_set_plane_interleave", "dwls_graph_replays", "dwls_transfer_bytes", "dwls_filter_host", "dwls_filter_batch_dev",
+           "dwls_kernel_launches", "dwls_set_group_frames", "dwls_set_lanes", "dwls_set_kernel_timing", "dwls_kernel_timing_report", "dwls_set_cuda_graphs", "dwls_set_plane_interleave", "dwls_graph_replays", "dwls_transfer_bytes", "dwls_filter_host", "dwls_filter_batch_dev",
            "dwls_filter_batch_host", "dwls_fgs_host", "dwls_fgs_dev", "dwls_lrc_mask_host", "dwls_fgs_weights_host"]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -87,6 +87,7 @@ def lib():
             L.dwls_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
             L.dwls_ctx_destroy.argtypes = [C.c_void_p]
             L.dwls_set_group_frames.argtypes = [C.c_void_p, C.c_int]
+            L.dwls_set_lanes.argtypes = [C.c_void_p, C.c_int]
             L.dwls_set_kernel_timing.argtypes = [C.c_void_p, C.c_int]
             L.dwls_set_cuda_graphs.argtypes = [C.c_void_p, C.c_int]
             L.dwls_set_plane_interleave.argtypes = [C.c_void_p, C.c_int]
@@ -144,6 +145,9 @@ class Context:
 
     def set_group_frames(self, n):
         self.check(lib().dwls_set_group_frames(self._h, int(n)))
+
+    def set_lanes(self, n):
+        self.check(lib().dwls_set_lanes(self._h, int(n)))
 
     def set_plane_interleave(self, on):
         self.check(lib().dwls_set_plane_interleave(self._h, int(bool(on))))

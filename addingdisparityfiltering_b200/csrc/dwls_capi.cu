@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <atomic>
 #include <mutex>
+#include <condition_variable>
 #include <string>
 #include <thread>
 #include <vector>
@@ -21,6 +22,60 @@
 #include "dwls_resize.cuh"
 
 using namespace dwls;
+
+constexpr int DWLS_MAX_LANES = 4;
+
+// persistent host workers of a context (staging copies of the single-call host entry points): started on first use,
+// parked on a condition variable between calls, joined when the context is destroyed
+class WorkerPool {
+    std::vector<std::thread> th_;
+    std::mutex m_;
+    std::condition_variable cv_, done_;
+    const std::function<void(int)>* job_ = nullptr;
+    uint64_t gen_ = 0;
+    int pending_ = 0;
+    bool stop_ = false;
+    void loop(int id)
+    {
+        uint64_t seen = 0;
+        for (;;) {
+            const std::function<void(int)>* job;
+            {
+                std::unique_lock<std::mutex> lk(m_);
+                cv_.wait(lk, [&] { return stop_ || gen_ != seen; });
+                if (stop_) return;
+                seen = gen_;
+                job = job_;
+            }
+            (*job)(id);
+            {
+                std::lock_guard<std::mutex> lk(m_);
+                if (--pending_ == 0) done_.notify_one();
+            }
+        }
+    }
+
+public:
+    // f(0) on the calling thread, f(1) .. f(n-1) on the workers; returns when all have finished
+    void run(int n, const std::function<void(int)>& f)
+    {
+        while ((int)th_.size() < n - 1) { const int id = (int)th_.size() + 1; th_.emplace_back([this, id] { loop(id); }); }
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            job_ = &f; pending_ = n - 1; ++gen_;
+        }
+        cv_.notify_all();
+        f(0);
+        std::unique_lock<std::mutex> lk(m_);
+        done_.wait(lk, [&] { return pending_ == 0; });
+    }
+    ~WorkerPool()
+    {
+        { std::lock_guard<std::mutex> lk(m_); stop_ = true; }
+        cv_.notify_all();
+        for (auto& t : th_) t.join();
+    }
+};
 
 struct dwls_ctx {
     int device = 0;
@@ -38,6 +93,7 @@ struct dwls_ctx {
     // pinned host staging of the single-call entry points: pageable caller memory is copied into it by a few host threads,
     // each feeding its own copy stream (the driver's own pageable path is single-threaded)
     void* hpin = nullptr; size_t hpin_bytes = 0;
+    WorkerPool pool;
     cudaStream_t xs[8] = {};
     cudaEvent_t xe[8][2] = {};
     cudaEvent_t xready = nullptr;
@@ -64,6 +120,18 @@ struct dwls_ctx {
     // device entry point records `busy` on its stream when it has queued its work, and the next one waits for it when it
     // runs on another stream (same stream: already ordered).
     cudaEvent_t busy = nullptr; cudaStream_t busy_stream = nullptr; bool busy_valid = false;
+    // device batch entry point: launch groups are dealt round-robin to `lanes` internal streams (forked from and joined
+    // back into the caller's stream), each with its own workspace slice, so that the tail of one group's kernels overlaps
+    // the head of another's; with small groups the planes a group hands from kernel to kernel stay in the 126 MB L2
+    int lanes = 1;
+    cudaStream_t lane_st[DWLS_MAX_LANES] = {};
+    cudaEvent_t lane_ev[DWLS_MAX_LANES] = {};
+    cudaEvent_t fork_ev = nullptr;
+    // host-side launch set-up that does not change between calls: encoded tensor maps and occupancy answers
+    struct TmapKey { const void* base; int pitch; int64_t rows; int bc, br; bool operator==(const TmapKey& o) const { return base == o.base && pitch == o.pitch && rows == o.rows && bc == o.bc && br == o.br; } };
+    std::vector<std::pair<TmapKey, CUtensorMap>> tmaps;       // small LRU-less cache, cleared when the workspace moves
+    struct VCache { int per_sm = 0; size_t smem = 0; int threads = 0; };
+    std::unordered_map<const void*, VCache> vcache;
 };
 
 // orders a call on `st` after the previous call's work (see dwls_ctx::busy)
@@ -127,6 +195,7 @@ static dwls_status ensure(dwls_ctx* ctx, void** p, size_t* have, size_t need)
         CK(cudaDeviceSynchronize());
         for (auto& ge : ctx->graph_cache) cudaGraphExecDestroy(ge.exec);      // cached graphs point into the old allocation
         ctx->graph_cache.clear();
+        ctx->tmaps.clear();
         CK(cudaFree(*p)); *p = nullptr; *have = 0;
     }
     CK(cudaMalloc(p, need));
@@ -185,6 +254,8 @@ void dwls_ctx_destroy(dwls_ctx* ctx)
     }
     if (ctx->xready) cudaEventDestroy(ctx->xready);
     if (ctx->busy) cudaEventDestroy(ctx->busy);
+    for (int l = 0; l < DWLS_MAX_LANES; ++l) { if (ctx->lane_st[l]) cudaStreamDestroy(ctx->lane_st[l]); if (ctx->lane_ev[l]) cudaEventDestroy(ctx->lane_ev[l]); }
+    if (ctx->fork_ev) cudaEventDestroy(ctx->fork_ev);
     for (auto& sp : ctx->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto e : ctx->free_events) cudaEventDestroy(e);
     delete ctx;
@@ -196,6 +267,13 @@ dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames)
 {
     if (!ctx || frames < 0) return DWLS_BAD_ARG;
     ctx->group_frames = frames;
+    return DWLS_OK;
+}
+
+dwls_status dwls_set_lanes(dwls_ctx* ctx, int lanes)
+{
+    if (!ctx || lanes < 1 || lanes > DWLS_MAX_LANES) return DWLS_BAD_ARG;
+    ctx->lanes = lanes;
     return DWLS_OK;
 }
 
@@ -344,7 +422,18 @@ static EncodeTiledFn get_encode()
 }
 
 // 2-D fp32 tensor [rows][pitch] with a (box_rows x box_cols) tile
+static dwls_status make_tmap_uncached(dwls_ctx* ctx, CUtensorMap* tm, const float* base, int pitch, int64_t rows, int box_cols, int box_rows);
 static dwls_status make_tmap(dwls_ctx* ctx, CUtensorMap* tm, const float* base, int pitch, int64_t rows, int box_cols, int box_rows)
+{
+    const dwls_ctx::TmapKey key = { base, pitch, rows, box_cols, box_rows };
+    for (auto& e : ctx->tmaps) if (e.first == key) { *tm = e.second; return DWLS_OK; }
+    const dwls_status s = make_tmap_uncached(ctx, tm, base, pitch, rows, box_cols, box_rows);
+    if (s) return s;
+    if (ctx->tmaps.size() >= 256) ctx->tmaps.erase(ctx->tmaps.begin(), ctx->tmaps.begin() + 128);
+    ctx->tmaps.push_back({ key, *tm });
+    return DWLS_OK;
+}
+static dwls_status make_tmap_uncached(dwls_ctx* ctx, CUtensorMap* tm, const float* base, int pitch, int64_t rows, int box_cols, int box_rows)
 {
     if (!get_encode()) return fail(ctx, DWLS_CUDA_ERROR, "cuTensorMapEncodeTiled is not available in this driver");
     const cuuint64_t dims[2] = { (cuuint64_t)pitch, (cuuint64_t)rows };
@@ -373,7 +462,14 @@ static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
     const size_t smem = vsolve_smem_bytes<M, S, VC>(pl.vK, g.nb * g.rb, WB ? 2 : 1);
     if (smem > 227 * 1024) return fail(ctx, DWLS_UNSUPPORTED, "image too tall for the shared-memory stage of the column pass");
     auto k = vsolve_kernel<M, S, VC, FIN, MAXT, WB, IL>;
-    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dwls_ctx::VCache& vc = ctx->vcache[(const void*)k];
+    if (!vc.per_sm || vc.smem != smem || vc.threads != VC * pl.vK) {
+        int per_sm = 1;
+        CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, VC * pl.vK, smem));
+        if (per_sm < 1) return fail(ctx, DWLS_CUDA_ERROR, "column pass does not fit on an SM");
+        vc.per_sm = per_sm; vc.smem = smem; vc.threads = VC * pl.vK;
+    }
     CUtensorMap tw, t0, t1;
     dwls_status s;
     const int64_t rows = (int64_t)frames * a.h;           // frames are contiguous planes: a.p_frame == a.w_frame == pitch * h
@@ -385,10 +481,7 @@ static dwls_status launch_v_inst(dwls_ctx* ctx, const SolveArgs& a, const SolveP
         if (S > 1) { if ((s = make_tmap(ctx, &t1, a.in[1], a.pitch, rows, VC, g.rb))) return s; }
         else t1 = t0;
     }
-    int per_sm = 1;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, VC * pl.vK, smem));
-    if (per_sm < 1) return fail(ctx, DWLS_CUDA_ERROR, "column pass does not fit on an SM");
-    int grid = ctx->num_sms * per_sm;
+    int grid = ctx->num_sms * vc.per_sm;
     if (grid > g.strips_total) grid = g.strips_total;
     TIMED(FIN == FIN_FLOAT ? K_VSOLVE : K_VSOLVE_FIN, st, k<<<grid, VC * pl.vK, smem, st>>>(a, g, tw, t0, t1));
     CK(cudaGetLastError());
@@ -854,13 +947,34 @@ extern "C" dwls_status dwls_filter_batch_dev(dwls_ctx* ctx, const dwls_batch* b,
     cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
     const WsLayout L = ws_layout(g, p->use_confidence != 0);
     const int G = pick_group(ctx, L.per_frame * sizeof(float), b->n_frames);
-    if ((s = ensure(ctx, &ctx->ws, &ctx->ws_bytes, align256((size_t)G * L.per_frame * sizeof(float))))) return s;
+    const int groups = (b->n_frames + G - 1) / G;
+    const int lanes = ctx->timing ? 1 : std::min(ctx->lanes, groups);     // per-kernel timing wants the kernels one after another
+    const size_t lane_ws = align256((size_t)G * L.per_frame * sizeof(float));
+    if ((s = ensure(ctx, &ctx->ws, &ctx->ws_bytes, lanes * lane_ws))) return s;
     CK(call_enter(ctx, st));
     if ((s = ensure_lut(ctx, (float)p->sigma_color, st))) return s;
-    for (int f0 = 0; f0 < b->n_frames; f0 += G) {
-        const int nf = (b->n_frames - f0 < G) ? b->n_frames - f0 : G;
-        if ((s = filter_frames_graphed(ctx, b, f0, nf, g, p, roi_in, st))) return s;
+    if (lanes > 1) {
+        if (!ctx->fork_ev) CK(cudaEventCreateWithFlags(&ctx->fork_ev, cudaEventDisableTiming));
+        CK(cudaEventRecord(ctx->fork_ev, st));
+        for (int l = 0; l < lanes; ++l) {
+            if (!ctx->lane_st[l]) {
+                CK(cudaStreamCreateWithFlags(&ctx->lane_st[l], cudaStreamNonBlocking));
+                CK(cudaEventCreateWithFlags(&ctx->lane_ev[l], cudaEventDisableTiming));
+            }
+            CK(cudaStreamWaitEvent(ctx->lane_st[l], ctx->fork_ev, 0));
+        }
     }
+    int gi = 0;
+    for (int f0 = 0; f0 < b->n_frames; f0 += G, ++gi) {
+        const int nf = (b->n_frames - f0 < G) ? b->n_frames - f0 : G;
+        const int l = gi % lanes;
+        if ((s = filter_frames_graphed(ctx, b, f0, nf, g, p, roi_in, lanes > 1 ? ctx->lane_st[l] : st, (float*)((uint8_t*)ctx->ws + l * lane_ws)))) return s;
+    }
+    if (lanes > 1)
+        for (int l = 0; l < lanes; ++l) {
+            CK(cudaEventRecord(ctx->lane_ev[l], ctx->lane_st[l]));
+            CK(cudaStreamWaitEvent(st, ctx->lane_ev[l], 0));
+        }
     CK(call_leave(ctx, st));
     return DWLS_OK;
 }
@@ -924,7 +1038,7 @@ static dwls_status xfer_upload(dwls_ctx* ctx, XferJob* jobs, int n, cudaStream_t
         return DWLS_OK;
     }
     std::atomic<int> err(0);
-    auto work = [&](int t) {
+    const std::function<void(int)> work = [&](int t) {
         if (cudaSetDevice(ctx->device) != cudaSuccess) { err = 1; return; }
         for (int i = 0; i < n; ++i) {
             const XferJob& j = jobs[i];
@@ -939,10 +1053,7 @@ static dwls_status xfer_upload(dwls_ctx* ctx, XferJob* jobs, int n, cudaStream_t
         }
         if (cudaEventRecord(ctx->xe[t][0], ctx->xs[t]) != cudaSuccess) err = 1;
     };
-    std::thread th[XFER_T - 1];
-    for (int t = 1; t < XFER_T; ++t) th[t - 1] = std::thread(work, t);
-    work(0);
-    for (int t = 1; t < XFER_T; ++t) th[t - 1].join();
+    ctx->pool.run(XFER_T, work);
     if (err) { cudaGetLastError(); return fail(ctx, DWLS_CUDA_ERROR, "host-to-device staging copy failed"); }
     for (int t = 0; t < XFER_T; ++t) CK(cudaStreamWaitEvent(st, ctx->xe[t][0], 0));
     return DWLS_OK;
@@ -962,7 +1073,7 @@ static dwls_status xfer_download(dwls_ctx* ctx, XferJob* jobs, int n, cudaStream
     }
     CK(cudaEventRecord(ctx->xready, st));
     std::atomic<int> err(0);
-    auto work = [&](int t) {
+    const std::function<void(int)> work = [&](int t) {
         if (cudaSetDevice(ctx->device) != cudaSuccess || cudaStreamWaitEvent(ctx->xs[t], ctx->xready, 0) != cudaSuccess) { err = 1; return; }
         // the chunks of this thread's slabs, two in flight: chunk c+1 is being copied while chunk c is moved to the caller
         struct Chunk { int job, r0, r1; };
@@ -986,10 +1097,7 @@ static dwls_status xfer_download(dwls_ctx* ctx, XferJob* jobs, int n, cudaStream
             xfer_rows(jobs[ch[c].job], (uint8_t*)ctx->hpin, ch[c].r0, ch[c].r1, false);
         }
     };
-    std::thread th[XFER_T - 1];
-    for (int t = 1; t < XFER_T; ++t) th[t - 1] = std::thread(work, t);
-    work(0);
-    for (int t = 1; t < XFER_T; ++t) th[t - 1].join();
+    ctx->pool.run(XFER_T, work);
     if (err) { cudaGetLastError(); return fail(ctx, DWLS_CUDA_ERROR, "device-to-host staging copy failed"); }
     CK(cudaStreamSynchronize(st));
     return DWLS_OK;

@@ -298,6 +298,7 @@ def main():
     ap.add_argument("--tail-min", type=int, default=-1, help="smallest halved tail chunk (-1 = 0 on one GPU, 4 on several)")
     ap.add_argument("--gather-mode", default="root", choices=["root", "all"])
     ap.add_argument("--group", type=int, default=0, help="frames per kernel launch group inside a chunk (0 = library default)")
+    ap.add_argument("--lanes", type=int, default=0, help="internal streams the launch groups of a chunk are dealt to (0 = library default)")
     ap.add_argument("--e2e-frames", type=int, default=64, help="frames per rank and step of the end-to-end (host buffer) leg")
     ap.add_argument("--ref-frames", type=int, default=4)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
@@ -325,6 +326,8 @@ def main():
         ctx.set_group_frames(args.group)
     if args.interleave:
         ctx.set_plane_interleave(True)
+    if args.lanes:
+        ctx.set_lanes(args.lanes)
     chunk = args.chunk or default_chunk(world)
     tail_min = args.tail_min if args.tail_min >= 0 else (0 if world == 1 else 4)
 

@@ -95,6 +95,9 @@ DWLS_API void        dwls_transfer_bytes(const dwls_ctx* ctx, int64_t* h2d, int6
  * (faster column pass, slower row pass: measured a net loss).  Results are identical either way; the
  * switch exists for A/B measurements and tests. */
 DWLS_API dwls_status dwls_set_plane_interleave(dwls_ctx* ctx, int on);
+/* dwls_filter_batch_dev deals its launch groups round-robin to `lanes` (1..4) internal streams forked from / joined into
+ * the caller's stream, each lane with its own workspace slice (default 1: every group on the caller's stream). */
+DWLS_API dwls_status dwls_set_lanes(dwls_ctx* ctx, int lanes);
 /* frames processed per kernel launch group in the batch entry point (0 = choose automatically) */
 DWLS_API dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames);
 
