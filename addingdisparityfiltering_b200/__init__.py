@@ -8,3 +8,4 @@ from ._lib import Context, DwlsError, build, default_context, lib  # noqa: F401
 from .ximgproc import (DisparityWLSFilter, FastGlobalSmootherFilter, computeBadPixelPercent, computeMSE,  # noqa: F401
                        createDisparityWLSFilter, createDisparityWLSFilterGeneric, createFastGlobalSmootherFilter,
                        createRightMatcher, fastGlobalSmootherFilter, fgs_weights, getDisparityVis, readGT)
+from .stereo import StereoBM  # noqa: F401,E402

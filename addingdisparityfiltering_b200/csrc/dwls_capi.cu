@@ -20,6 +20,7 @@
 
 #include "../../include/dwls_b200.h"
 #include "dwls_resize.cuh"
+#include "dwls_stereo.cuh"
 
 using namespace dwls;
 
@@ -90,6 +91,8 @@ struct dwls_ctx {
     float* lut = nullptr; float lut_sigma = -1.f;           // per-sigma LUT cache (fgs_filter.cpp:150-154)
     void* ws = nullptr; size_t ws_bytes = 0;                // solver workspace (grow-only)
     void* stage = nullptr; size_t stage_bytes = 0;          // device staging of the host entry points
+    void* bmws = nullptr; size_t bmws_bytes = 0;            // stereo matcher: prefiltered views
+    void* bmstage = nullptr; size_t bmstage_bytes = 0;      // stereo matcher: staging of its host entry point
     // pinned host staging of the single-call entry points: pageable caller memory is copied into it by a few host threads,
     // each feeding its own copy stream (the driver's own pageable path is single-threaded)
     void* hpin = nullptr; size_t hpin_bytes = 0;
@@ -147,10 +150,12 @@ static cudaError_t call_leave(dwls_ctx* ctx, cudaStream_t st)
     return cudaEventRecord(ctx->busy, st);
 }
 
-enum KernelId { K_LUT = 0, K_WEIGHTS, K_CONF_R, K_CONF_L, K_UPSCALE, K_PREP, K_FILL, K_HSOLVE, K_VSOLVE, K_VSOLVE_FIN, K_UNPACK, K_PACK, K_TRANSPOSE, K_COUNT };
+enum KernelId { K_LUT = 0, K_WEIGHTS, K_CONF_R, K_CONF_L, K_UPSCALE, K_PREP, K_FILL, K_HSOLVE, K_VSOLVE, K_VSOLVE_FIN, K_UNPACK, K_PACK, K_TRANSPOSE,
+                K_BM_PREF, K_BM, K_BM_FILL, K_HALF, K_COUNT };
 static const char* const kKernelNames[K_COUNT] = { "lut_kernel", "weights_kernel", "conf_kernel<right>", "conf_kernel<left+lrc>", "upscale_prep_kernel",
                                                    "prep_noconf_kernel", "border_kernel", "hsolve_kernel", "vsolve_kernel", "vsolve_kernel<final>",
-                                                   "unpack_kernel", "pack_kernel", "transpose_kernel" };
+                                                   "unpack_kernel", "pack_kernel", "transpose_kernel", "bm_prefilter_kernel", "bm_kernel", "bm_fill_kernel",
+                                                   "half_kernel" };
 
 // counts the launch and, when timing is on, brackets it with CUDA events on the launching stream
 struct KTimer {
@@ -246,7 +251,7 @@ void dwls_ctx_destroy(dwls_ctx* ctx)
     if (ctx->stream2) { cudaStreamSynchronize(ctx->stream2); cudaStreamDestroy(ctx->stream2); }
     for (auto& ge : ctx->graph_cache) cudaGraphExecDestroy(ge.exec);
     if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
-    cudaFree(ctx->lut); cudaFree(ctx->ws); cudaFree(ctx->stage);
+    cudaFree(ctx->lut); cudaFree(ctx->ws); cudaFree(ctx->stage); cudaFree(ctx->bmws); cudaFree(ctx->bmstage);
     if (ctx->hpin) cudaFreeHost(ctx->hpin);
     for (int t = 0; t < 8; ++t) {
         if (ctx->xs[t]) cudaStreamDestroy(ctx->xs[t]);
@@ -1473,5 +1478,147 @@ extern "C" dwls_status dwls_filter_batch_host(dwls_ctx* ctx, const dwls_batch* h
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream2));
     ctx->busy_valid = false;                 // nothing of this ctx is in flight any more
+    return DWLS_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// stereo block matching on the device: the producer of the filter's inputs.
+// Reference call sites: samples/disparity_filtering.cpp:148-160 (StereoBM::create(max_disp, wsize), createRightMatcher,
+// compute(left, right) / compute(right, left)) under the parameter contract of src/disparity_filters.cpp:389-403, 419-428.
+// ---------------------------------------------------------------------------------------------
+extern "C" void dwls_bm_default_params(dwls_bm_params* p)
+{
+    if (!p) return;
+    p->num_disparities = 64; p->block_size = 21; p->min_disparity = 0;       // cv::StereoBM::create(0, 21)
+    p->pre_filter_cap = 31; p->texture_threshold = 10; p->uniqueness_ratio = 15;
+}
+
+static dwls_status bm_check(dwls_ctx* ctx, const dwls_bm_params* p, int w, int h, int cn)
+{
+    if (!p) return fail(ctx, DWLS_BAD_ARG, "matcher params is NULL");
+    if (cn != 1 && cn != 3) return fail(ctx, DWLS_BAD_ARG, "views must be CV_8UC1 (or CV_8UC3, converted like cvtColor BGR2GRAY)");
+    if (p->num_disparities <= 0 || p->num_disparities % 16) return fail(ctx, DWLS_BAD_ARG, "numDisparities must be positive and divisible by 16");   // StereoBM::compute
+    if (p->block_size < 5 || p->block_size > 255 || !(p->block_size & 1) || p->block_size >= (w < h ? w : h))
+        return fail(ctx, DWLS_BAD_ARG, "SADWindowSize must be odd, be within 5..255 and be not larger than image width or height");
+    if (p->pre_filter_cap < 1 || p->pre_filter_cap > 63) return fail(ctx, DWLS_BAD_ARG, "preFilterCap must be within 1..63");
+    if (p->min_disparity > 0) return fail(ctx, DWLS_UNSUPPORTED, "minDisparity > 0 is not supported by the device matcher (OpenCV itself writes past the row end there)");
+    if (p->texture_threshold < 0 || p->uniqueness_ratio < 0) return fail(ctx, DWLS_BAD_ARG, "texture threshold and uniqueness ratio must be non-negative");
+    if (p->block_size * p->block_size * 2 * p->pre_filter_cap >= 65536) return fail(ctx, DWLS_UNSUPPORTED, "window too large for the 16-bit SAD accumulators of the device matcher");
+    return DWLS_OK;
+}
+
+// prefilter both views, then match: view 0 = matcher(left, right) with p->min_disparity; view 1 (when disp_right) = the
+// matcher createRightMatcher builds: compute(right, left) with minDisparity -(min + num) + 1 (disparity_filters.cpp:424)
+static dwls_status bm_frames(dwls_ctx* ctx, const uint8_t* left, int64_t l_step, int64_t l_frame, const uint8_t* right, int64_t r_step, int64_t r_frame,
+                             int cn, int w, int h, int frames, const dwls_bm_params* p, int16_t* dl, int64_t dl_step, int64_t dl_frame,
+                             int16_t* dr, int64_t dr_step, int64_t dr_frame, cudaStream_t st)
+{
+    dwls_status s;
+    const size_t plane = align256((size_t)w * h);
+    if ((s = ensure(ctx, &ctx->bmws, &ctx->bmws_bytes, 2 * plane * frames))) return s;
+    uint8_t* pl = (uint8_t*)ctx->bmws; uint8_t* pr = pl + plane * frames;
+    PrefArgs pa;
+    memset(&pa, 0, sizeof pa);
+    pa.src[0] = left; pa.s_step[0] = l_step; pa.s_frame[0] = l_frame; pa.src[1] = right; pa.s_step[1] = r_step; pa.s_frame[1] = r_frame; pa.cn = cn;
+    pa.dst[0] = pl; pa.dst[1] = pr; pa.d_step = w; pa.d_frame = (int64_t)plane; pa.w = w; pa.h = h; pa.cap = p->pre_filter_cap;
+    TIMED(K_BM_PREF, st, bm_prefilter_kernel<<<dim3((w + 255) / 256, h, 2 * frames), 256, 0, st>>>(pa));
+    CK(cudaGetLastError());
+    BmArgs a0, a1;
+    memset(&a0, 0, sizeof a0);
+    a0.left = pl; a0.l_step = w; a0.l_frame = (int64_t)plane; a0.right = pr; a0.r_step = w; a0.r_frame = (int64_t)plane;
+    a0.disp = dl; a0.d_step = dl_step; a0.d_frame = dl_frame; a0.w = w; a0.h = h;
+    a0.ndisp = p->num_disparities; a0.wsz = p->block_size; a0.mindisp = p->min_disparity; a0.ftzero = p->pre_filter_cap;
+    a0.texture = p->texture_threshold; a0.uniq = p->uniqueness_ratio;
+    a1 = a0;
+    const int views = dr ? 2 : 1;
+    if (dr) {
+        a1.left = pr; a1.right = pl; a1.disp = dr; a1.d_step = dr_step; a1.d_frame = dr_frame;
+        a1.mindisp = -(p->min_disparity + p->num_disparities) + 1;
+    }
+    const BmPlan P0 = bm_plan(w, h, a0.ndisp, a0.wsz, a0.mindisp), P1 = bm_plan(w, h, a1.ndisp, a1.wsz, a1.mindisp);
+    // frames * 2 blocks in z even for one view (the odd ones return at once): keeps the view / frame decoding in one place
+    TIMED(K_BM_FILL, st, bm_fill_kernel<<<dim3((w + 255) / 256, h, 2 * frames), 256, 0, st>>>(a0, dr ? a1 : a0));
+    CK(cudaGetLastError());
+    const bool run0 = P0.lofs < w && P0.rofs < w && P0.width1 >= 1 && P0.y1 > P0.y0, run1 = dr && P1.lofs < w && P1.rofs < w && P1.width1 >= 1 && P1.y1 > P1.y0;
+    if (!run0 && !run1) return DWLS_OK;                                     // numDisparities wider than the image: everything is FILTERED
+    if ((run0 && !P0.ok) || (run1 && !P1.ok)) return fail(ctx, DWLS_UNSUPPORTED, "numDisparities x window too large for the device matcher's per-thread sums");
+    const int width1 = std::max(run0 ? P0.width1 : 0, run1 ? P1.width1 : 0);
+    const size_t smem = std::max(P0.smem, P1.smem);
+    if (smem > 200 * 1024) return fail(ctx, DWLS_UNSUPPORTED, "numDisparities x window too large for the device matcher's shared memory");
+    if (ctx->smem_attr_done.insert((const void*)bm_kernel).second || smem > 48 * 1024)
+        CK(cudaFuncSetAttribute(bm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    if (!run0) { a0 = a1; }                                                  // (cannot happen for a left matcher with a valid right one; kept total)
+    (void)views;
+    TIMED(K_BM, st, bm_kernel<<<dim3((width1 + BM_TW - 1) / BM_TW, (P0.y1 - P0.y0 + BM_RB - 1) / BM_RB, 2 * frames), BM_T, smem, st>>>(a0, run1 ? a1 : a0));
+    CK(cudaGetLastError());
+    return DWLS_OK;
+}
+
+extern "C" dwls_status dwls_stereo_bm_dev(dwls_ctx* ctx, const dwls_views* v, const dwls_bm_params* p, int16_t* disp_left, int64_t dl_step, int64_t dl_frame,
+                                          int16_t* disp_right, int64_t dr_step, int64_t dr_frame, void* stream)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    if (!v || v->n_frames <= 0 || !v->left || !v->right || v->cols <= 0 || v->rows <= 0 || !disp_left) return fail(ctx, DWLS_BAD_ARG, "views / output missing");
+    dwls_status s = bm_check(ctx, p, v->cols, v->rows, v->channels);
+    if (s) return s;
+    if ((dl_step | dl_frame | dr_step | dr_frame) & 1) return fail(ctx, DWLS_BAD_ARG, "CV_16S strides must be even");
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    CK(call_enter(ctx, st));
+    if ((s = bm_frames(ctx, v->left, v->left_step, v->left_frame, v->right, v->right_step, v->right_frame, v->channels, v->cols, v->rows, v->n_frames, p,
+                       disp_left, dl_step / 2, dl_frame / 2, disp_right, dr_step / 2, dr_frame / 2, st))) return s;
+    CK(call_leave(ctx, st));
+    return DWLS_OK;
+}
+
+extern "C" dwls_status dwls_stereo_bm_host(dwls_ctx* ctx, const dwls_image* left, const dwls_image* right, const dwls_bm_params* p,
+                                           dwls_image* disp_left, dwls_image* disp_right)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    if (!img_ok(left, DWLS_8U, 1, 3) || !img_ok(right, DWLS_8U, 1, 3) || left->rows != right->rows || left->cols != right->cols || left->channels != right->channels)
+        return fail(ctx, DWLS_BAD_ARG, "left and right views must be non-empty CV_8UC1 / CV_8UC3 images of equal size and type");    // StereoBM::compute
+    const int w = left->cols, h = left->rows, cn = left->channels;
+    dwls_status s = bm_check(ctx, p, w, h, cn);
+    if (s) return s;
+    if (!img_ok(disp_left, DWLS_16S, 1, 1) || disp_left->rows != h || disp_left->cols != w) return fail(ctx, DWLS_BAD_ARG, "disp_left must be a caller-allocated CV_16SC1 image of the view size");
+    if (disp_right && disp_right->data && (!img_ok(disp_right, DWLS_16S, 1, 1) || disp_right->rows != h || disp_right->cols != w))
+        return fail(ctx, DWLS_BAD_ARG, "disp_right must be CV_16SC1 of the view size");
+    const bool both = disp_right && disp_right->data;
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    CK(call_enter(ctx, st));
+    const size_t b_v = align256((size_t)w * h * cn), b_d = align256((size_t)w * h * 2);
+    if ((s = ensure(ctx, &ctx->bmstage, &ctx->bmstage_bytes, 2 * b_v + 2 * b_d))) return s;
+    uint8_t* d_l = (uint8_t*)ctx->bmstage; uint8_t* d_r = d_l + b_v; uint8_t* d_dl = d_r + b_v; uint8_t* d_dr = d_dl + b_d;
+    CK(cudaMemcpy2DAsync(d_l, (size_t)w * cn, left->data, (size_t)left->step, (size_t)w * cn, h, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpy2DAsync(d_r, (size_t)w * cn, right->data, (size_t)right->step, (size_t)w * cn, h, cudaMemcpyHostToDevice, st));
+    ctx->h2d_bytes += 2 * (int64_t)w * h * cn;
+    if ((s = bm_frames(ctx, d_l, (int64_t)w * cn, 0, d_r, (int64_t)w * cn, 0, cn, w, h, 1, p, (int16_t*)d_dl, w, 0, both ? (int16_t*)d_dr : nullptr, w, 0, st))) return s;
+    CK(cudaMemcpy2DAsync(disp_left->data, (size_t)disp_left->step, d_dl, (size_t)w * 2, (size_t)w * 2, h, cudaMemcpyDeviceToHost, st));
+    if (both) CK(cudaMemcpy2DAsync(disp_right->data, (size_t)disp_right->step, d_dr, (size_t)w * 2, (size_t)w * 2, h, cudaMemcpyDeviceToHost, st));
+    ctx->d2h_bytes += (both ? 2 : 1) * (int64_t)w * h * 2;
+    CK(cudaStreamSynchronize(st));
+    return DWLS_OK;
+}
+
+// views halved like the sample's downscale step (cv::resize(..., Size(), 0.5, 0.5), samples/disparity_filtering.cpp:138-139):
+// for even sizes bilinear interpolation at scale 0.5 is the rounded mean of each 2 x 2 block, (a + b + c + d + 2) >> 2
+extern "C" dwls_status dwls_halve_views_dev(dwls_ctx* ctx, const dwls_views* v, uint8_t* left_out, uint8_t* right_out, int64_t out_step, int64_t out_frame, void* stream)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    if (!v || v->n_frames <= 0 || !v->left || !v->right || !left_out || !right_out || (v->channels != 1 && v->channels != 3)) return fail(ctx, DWLS_BAD_ARG, "views / outputs missing");
+    if ((v->cols & 1) || (v->rows & 1) || v->cols < 2 || v->rows < 2) return fail(ctx, DWLS_UNSUPPORTED, "the device path halves even-sized views only");
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    CK(call_enter(ctx, st));
+    HalfArgs ha;
+    memset(&ha, 0, sizeof ha);
+    ha.src[0] = v->left; ha.s_step[0] = v->left_step; ha.s_frame[0] = v->left_frame; ha.src[1] = v->right; ha.s_step[1] = v->right_step; ha.s_frame[1] = v->right_frame;
+    ha.dst[0] = left_out; ha.dst[1] = right_out; ha.d_step = out_step; ha.d_frame = out_frame; ha.w = v->cols / 2; ha.h = v->rows / 2; ha.cn = v->channels;
+    const int nb = ha.w * ha.cn;
+    TIMED(K_HALF, st, half_kernel<<<dim3((nb + 255) / 256, ha.h, 2 * v->n_frames), 256, 0, st>>>(ha));
+    CK(cudaGetLastError());
+    CK(call_leave(ctx, st));
     return DWLS_OK;
 }

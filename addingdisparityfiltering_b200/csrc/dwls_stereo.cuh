@@ -1,0 +1,291 @@
+// dwls_stereo.cuh — block-matching stereo on the device (the step that PRODUCES the filter's inputs, so that
+// the disparity maps are born in HBM instead of crossing PCIe).
+//
+// The reference takes its inputs from cv::StereoBM (OpenCV calib3d, outside /root/reference: the sample calls
+// StereoBM::create(max_disp, wsize) + createRightMatcher, samples/disparity_filtering.cpp:148-160, under the parameter
+// contract of src/disparity_filters.cpp:389-403, 419-428).  calib3d's source is not in the reference tree; the algorithm
+// restated here is StereoBM's published one (x-Sobel prefilter with cap, SAD over a square window of the prefiltered
+// views, winner-takes-all with optional texture / uniqueness tests, parabola sub-pixel fit, valid-disparity rectangle),
+// pinned bit for bit against cv2.StereoBM.compute of the box's OpenCV 4.13 in tests/test_gpu_stereo.py (a numpy
+// restatement checked against cv2 on the CPU lives with the other test infrastructure).
+//
+// Integer arithmetic throughout: the CV_16S result is bit-exact.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dwls {
+
+struct BmArgs {
+    const uint8_t* left;  int64_t l_step, l_frame;       // prefiltered views (bytes)
+    const uint8_t* right; int64_t r_step, r_frame;
+    int16_t* disp; int64_t d_step, d_frame;               // elements
+    int w, h;
+    int ndisp, wsz, mindisp, ftzero, texture, uniq;
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// prefilter: optional BGR -> gray (cv::cvtColor 8U: (3735 B + 19235 G + 9798 R + 2^14) >> 15), then StereoBM's
+// PREFILTER_XSOBEL: rows are processed in pairs (y, y+1), y even, with the 1-2-1 column of x-differences taken over rows
+// (y-1, y, y+1) and (y, y+1, y+2); row -1 mirrors to row 1 and a missing row y+2 to row y; the first and last column and,
+// for an odd height, the last row hold the constant `cap`.  grid = (ceil(w/256), h, frames * views), block = 256
+// ---------------------------------------------------------------------------------------------------------------
+struct PrefArgs {
+    const uint8_t* src[2]; int64_t s_step[2], s_frame[2]; int cn;      // two views (left, right), 1 or 3 channels
+    uint8_t* dst[2]; int64_t d_step, d_frame;
+    int w, h, cap;
+};
+
+__device__ __forceinline__ int bm_gray(const uint8_t* p, int cn)
+{
+    return cn == 1 ? (int)p[0] : (int)((3735u * p[0] + 19235u * p[1] + 9798u * p[2] + 16384u) >> 15);
+}
+
+__global__ void __launch_bounds__(256) bm_prefilter_kernel(const PrefArgs a)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, v = blockIdx.z & 1, frame = blockIdx.z >> 1;
+    if (x >= a.w) return;
+    uint8_t* d = a.dst[v] + (size_t)frame * a.d_frame + (size_t)y * a.d_step + x;
+    const bool paired = y < ((a.h - 1) & ~1) || ((a.h & 1) == 0);          // every row but the last one of an odd height
+    if (x == 0 || x == a.w - 1 || !paired) { *d = (uint8_t)a.cap; return; }
+    const uint8_t* s = a.src[v] + (size_t)frame * a.s_frame[v];
+    const int ye = y & ~1;                                                   // the even row of this pair
+    int r0, r1, r2;                                                          // rows weighted 1, 2, 1
+    if (y == ye) { r1 = ye; r0 = ye > 0 ? ye - 1 : ye + 1; r2 = ye + 1; }
+    else { r0 = ye; r1 = ye + 1; r2 = ye + 2 < a.h ? ye + 2 : ye; }
+    auto dx = [&](int r) {
+        const uint8_t* p = s + (size_t)r * a.s_step[v] + (size_t)x * a.cn;
+        return bm_gray(p + a.cn, a.cn) - bm_gray(p - a.cn, a.cn);
+    };
+    const int val = dx(r0) + 2 * dx(r1) + dx(r2);
+    *d = (uint8_t)(min(max(val, -a.cap), a.cap) + a.cap);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// SAD block matching + winner-takes-all + sub-pixel fit.
+// A CTA owns BM_TW output columns x BM_RB rows.  Window column c of the tile (c = 0 .. BM_TW + wsz - 2) stands for the
+// left column cl[c] and the right base column cr[c] (both clamped like StereoBM clamps them; candidate d reads right
+// column cr[c] + d, i.e. disparity ndisp - 1 - d + mindisp).  For every row the CTA
+//   A. updates the vertical window sums V[c][d] = sum over the wsz rows of |L - R| (row entering minus row leaving; the
+//      sums live in registers, two 16-bit sums per register, four d per thread and step),
+//   B. publishes them to shared memory,
+//   C. forms SAD[x][d] = sum_{c = x .. x + wsz - 1} V[c][d] (thread = (x, quarter of the d range)), keeps the first minimum,
+//   D. merges the four quarters, applies the texture / uniqueness tests and the parabola fit, and stores the CV_16S value.
+// Pixels outside StereoBM's valid-disparity rectangle get FILTERED = (mindisp - 1) * 16.
+// grid = (ceil(width1 / BM_TW), ceil(valid rows / BM_RB), frames * 2 views), block = 256
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int BM_TW = 64, BM_RB = 32, BM_T = 256;
+constexpr int BM_MAXG = 16;      // (c, 4 d) groups a thread may own: (BM_TW + wsz - 1) * ndisp / 4 / BM_T <= BM_MAXG
+
+struct BmPlan { int lofs, rofs, width1, y0, y1, xmin, xmax, wc, np, vpitch, rw; size_t smem; bool ok; };
+
+__host__ __device__ inline BmPlan bm_plan(int w, int h, int ndisp, int wsz, int mindisp)
+{
+    BmPlan p;
+    const int n = ndisp - 1 + mindisp, w2 = wsz / 2;
+    p.lofs = n > 0 ? n : 0; p.rofs = n < 0 ? -n : 0;
+    p.width1 = w - p.rofs - ndisp + 1;
+    p.y0 = w2; p.y1 = h - w2;
+    const int maxd = mindisp + ndisp - 1;
+    p.xmin = (maxd > 0 ? maxd : 0) + w2;
+    p.xmax = (w < w - mindisp ? w : w - mindisp) - w2;
+    p.wc = BM_TW + wsz - 1;                     // window columns per tile
+    p.np = ndisp / 2;                           // packed pairs of d
+    p.vpitch = p.np | 1;                        // odd number of words per window column: conflict-free column walks
+    p.rw = (p.wc + ndisp + 3 + 3) & ~3;         // staged right row: wc + ndisp - 1 bytes (+ slack for word reads), multiple of 4
+    const int rows = BM_RB + wsz - 1;
+    p.smem = (size_t)rows * ((p.wc + 3) & ~3) + (size_t)rows * p.rw + (size_t)p.wc * p.vpitch * 4 + (size_t)p.wc * 4 * 3 + (size_t)BM_T * 8 + 64;
+    p.ok = p.lofs < w && p.rofs < w && p.width1 >= 1 && p.y1 > p.y0 && ndisp % 16 == 0 && ndisp >= 16 && (wsz & 1) && wsz >= 5 &&
+           (p.wc * (ndisp / 4) + BM_T - 1) / BM_T <= BM_MAXG;
+    return p;
+}
+
+__device__ __forceinline__ uint32_t bm_absdiff4(uint32_t l4, uint32_t r4) { return __vabsdiffu4(l4, r4); }
+
+__global__ void __launch_bounds__(BM_T) bm_kernel(const BmArgs a0, const BmArgs a1)
+{
+    extern __shared__ __align__(16) uint8_t bsm[];
+    const int view = blockIdx.z & 1, frame = blockIdx.z >> 1;
+    if (view == 1 && a1.disp == a0.disp) return;              // one matcher only: the second view's blocks have nothing to do
+    const BmArgs& a = view ? a1 : a0;
+    const int w = a.w, h = a.h, ndisp = a.ndisp, wsz = a.wsz, w2 = wsz / 2;
+    const BmPlan P = bm_plan(w, h, ndisp, wsz, a.mindisp);
+    const int FILTERED = (a.mindisp - 1) * 16;
+    const int tid = threadIdx.x;
+    const int x0 = blockIdx.x * BM_TW;                        // relative output column (absolute = lofs + x)
+    const int yb = P.y0 + blockIdx.y * BM_RB;                 // first output row of the band
+    if (x0 >= P.width1 || yb >= P.y1) return;                 // (uniform) tiles of the other view's larger grid
+    const int rows_out = min(BM_RB, P.y1 - yb);
+    const int rows = rows_out + wsz - 1;                      // staged rows yb - w2 .. yb + rows_out - 1 + w2
+    const int lpitch = (P.wc + 3) & ~3;
+    uint8_t* Ls = bsm;                                         // [rows][lpitch]
+    uint8_t* Rs = Ls + (size_t)(BM_RB + wsz - 1) * lpitch;     // [rows][rw]
+    uint32_t* V2 = (uint32_t*)(Rs + (size_t)(BM_RB + wsz - 1) * P.rw);   // [wc][vpitch] packed pairs of 16-bit sums
+    int* roff = (int*)(V2 + (size_t)P.wc * P.vpitch);          // [wc] offset of cr[c] inside a staged right row
+    int* T = roff + P.wc;                                      // [wc] vertical texture sums
+    int* spare = T + P.wc;                                     // [wc]
+    int2* red = (int2*)(((uintptr_t)(spare + P.wc) + 7) & ~(uintptr_t)7);   // [BM_T] (minsad, mind) per thread
+    const uint8_t* Lg = a.left + (size_t)frame * a.l_frame;
+    const uint8_t* Rg = a.right + (size_t)frame * a.r_frame;
+    int16_t* Dg = a.disp + (size_t)frame * a.d_frame;
+
+    // ---- stage the band: window column c <-> relative column xr = x0 - w2 + c ----
+    const int xr0 = x0 - w2;
+    auto colL = [&](int c) { return min(max(xr0 + c, -P.lofs), w - P.lofs - 1) + P.lofs; };
+    auto colR = [&](int c) { return min(max(xr0 + c, -P.rofs), w - P.rofs - ndisp) + P.rofs; };
+    const int rbase = colR(0);                                 // cr[] is non-decreasing: staged right columns rbase ..
+    const int rcols = colR(P.wc - 1) + ndisp - rbase;          // .. rbase + rcols - 1  (<= wc + ndisp - 1)
+    for (int c = tid; c < P.wc; c += BM_T) roff[c] = colR(c) - rbase;
+    for (int idx = tid; idx < rows * P.wc; idx += BM_T) {
+        const int r = idx / P.wc, c = idx - r * P.wc;
+        Ls[r * lpitch + c] = Lg[(size_t)(yb - w2 + r) * a.l_step + colL(c)];
+    }
+    for (int idx = tid; idx < rows * P.rw; idx += BM_T) {
+        const int r = idx / P.rw, j = idx - r * P.rw;
+        Rs[r * P.rw + j] = j < rcols ? Rg[(size_t)(yb - w2 + r) * a.r_step + rbase + j] : (uint8_t)0;
+    }
+    __syncthreads();
+
+    // ---- groups of (window column, 4 candidates) owned by this thread ----
+    const int nd4 = ndisp >> 2, ngroups = P.wc * nd4;
+    uint32_t v01[BM_MAXG], v23[BM_MAXG];                       // 16-bit vertical sums of candidates d, d+1 | d+2, d+3
+#pragma unroll
+    for (int k = 0; k < BM_MAXG; ++k) { v01[k] = 0; v23[k] = 0; }
+    auto diff4 = [&](int r, int c, int d) {                   // |L - R| for candidates d .. d+3 of window column c, staged row r
+        const uint32_t l4 = (uint32_t)Ls[r * lpitch + c] * 0x01010101u;
+        const uint8_t* rp = Rs + r * P.rw + roff[c] + d;
+        const uint32_t* wp = (const uint32_t*)((uintptr_t)rp & ~(uintptr_t)3);
+        const uint32_t r4 = __funnelshift_r(wp[0], wp[1], (int)(((uintptr_t)rp & 3) * 8));
+        return bm_absdiff4(l4, r4);
+    };
+    const bool want_tex = a.texture > 0;
+    int tsum_c = 0;                                            // this thread's texture column (tid < wc)
+    // warm-up: the first wsz - 1 rows of the window of output row yb
+    for (int r = 0; r < wsz - 1; ++r) {
+#pragma unroll
+        for (int k = 0; k < BM_MAXG; ++k) {
+            const int gi = tid + k * BM_T;
+            if (gi < ngroups) {
+                const int c = gi / nd4, d = (gi - c * nd4) * 4;
+                const uint32_t df = diff4(r, c, d);
+                v01[k] += __byte_perm(df, 0, 0x4140); v23[k] += __byte_perm(df, 0, 0x4342);
+            }
+        }
+        if (want_tex && tid < P.wc) tsum_c += abs((int)Ls[r * lpitch + tid] - a.ftzero);
+    }
+
+    const int xq = tid & (BM_TW - 1), q = tid / BM_TW;         // phase C: output column of the tile, quarter of the d range
+    const int dq0 = q * (ndisp / 4), dq1 = dq0 + ndisp / 4;    // candidates of this quarter (multiples of 4)
+    auto sad_at = [&](int x, int d) {                          // SAD of candidate d at tile column x from the published sums
+        int s = 0;
+        for (int c = x; c < x + wsz; ++c) { const uint32_t v = V2[c * P.vpitch + (d >> 1)]; s += (d & 1) ? (int)(v >> 16) : (int)(v & 0xffffu); }
+        return s;
+    };
+
+    for (int yo = 0; yo < rows_out; ++yo) {
+        // A. row yo + wsz - 1 enters; row yo - 1 leaves (after the first output row)
+#pragma unroll
+        for (int k = 0; k < BM_MAXG; ++k) {
+            const int gi = tid + k * BM_T;
+            if (gi < ngroups) {
+                const int c = gi / nd4, d = (gi - c * nd4) * 4;
+                const uint32_t dn = diff4(yo + wsz - 1, c, d);
+                v01[k] += __byte_perm(dn, 0, 0x4140); v23[k] += __byte_perm(dn, 0, 0x4342);
+                if (yo > 0) {
+                    const uint32_t dl = diff4(yo - 1, c, d);
+                    v01[k] -= __byte_perm(dl, 0, 0x4140); v23[k] -= __byte_perm(dl, 0, 0x4342);
+                }
+                // B. publish (sums stay below 2^16: wsz^2 * 2 * cap <= 21 * 21 * 126 < 65536, checked on the host)
+                V2[c * P.vpitch + (d >> 1)] = v01[k]; V2[c * P.vpitch + (d >> 1) + 1] = v23[k];
+            }
+        }
+        if (want_tex && tid < P.wc) {
+            tsum_c += abs((int)Ls[(yo + wsz - 1) * lpitch + tid] - a.ftzero);
+            if (yo > 0) tsum_c -= abs((int)Ls[(yo - 1) * lpitch + tid] - a.ftzero);
+            T[tid] = tsum_c;
+        }
+        __syncthreads();
+        // C. first minimum over this quarter's candidates
+        int minsad = 0x7fffffff, mind = -1;
+        for (int d = dq0; d < dq1; d += 2) {
+            uint32_t s2 = 0;
+            for (int c = xq; c < xq + wsz; ++c) s2 += V2[c * P.vpitch + (d >> 1)];     // both 16-bit halves at once (no carry: see B)
+            const int s0 = (int)(s2 & 0xffffu), s1 = (int)(s2 >> 16);
+            if (s0 < minsad) { minsad = s0; mind = d; }
+            if (s1 < minsad) { minsad = s1; mind = d + 1; }
+        }
+        red[tid] = make_int2(minsad, mind);
+        __syncthreads();
+        // D. merge the quarters (ascending d, strict <: the first minimum wins), tests, sub-pixel fit, store
+        const int xrel = x0 + xq, xabs = P.lofs + xrel, y = yb + yo;
+        bool filtered = false;
+        int best = 0x7fffffff, bd = -1;
+        if (q == 0 && xrel < P.width1) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { const int2 m = red[xq + k * BM_TW]; if (m.x < best) { best = m.x; bd = m.y; } }
+            if (want_tex) {
+                int ts = 0;
+                for (int c = xq; c < xq + wsz; ++c) ts += T[c];
+                filtered = ts < a.texture;
+            }
+        }
+        if (a.uniq > 0) {
+            // every quarter rescans its candidates against the merged minimum (uniform branch: a.uniq is a kernel argument)
+            int gb = 0x7fffffff, gd = -1;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { const int2 m = red[xq + k * BM_TW]; if (m.x < gb) { gb = m.x; gd = m.y; } }
+            const int thresh = gb + gb * a.uniq / 100;
+            int hit = 0;
+            for (int d = dq0; d < dq1; ++d)
+                if ((d < gd - 1 || d > gd + 1) && sad_at(xq, d) <= thresh) { hit = 1; break; }
+            __syncthreads();
+            red[tid] = make_int2(hit, 0);
+            __syncthreads();
+            if (q == 0) filtered |= (red[xq].x | red[xq + BM_TW].x | red[xq + 2 * BM_TW].x | red[xq + 3 * BM_TW].x) != 0;
+        }
+        if (q == 0 && xrel < P.width1) {
+            int val = FILTERED;
+            if (!filtered && xabs >= P.xmin && xabs < P.xmax) {
+                const int sp = sad_at(xq, bd + 1 < ndisp ? bd + 1 : ndisp - 2);         // sad[ndisp] = sad[ndisp - 2]
+                const int sn = sad_at(xq, bd > 0 ? bd - 1 : 1);                           // sad[-1] = sad[1]
+                const int dd = sp + sn - 2 * best + abs(sp - sn);
+                val = ((ndisp - bd - 1 + a.mindisp) * 256 + (dd != 0 ? (sp - sn) * 256 / dd : 0) + 15) >> 4;
+            }
+            Dg[(size_t)y * a.d_step + xabs] = (int16_t)val;
+        }
+        __syncthreads();                                       // V2 / T / red are rewritten by the next row
+    }
+}
+
+// everything the matcher does not compute: rows outside [y0, y1) and columns outside [lofs, lofs + width1)
+// grid = (ceil(w/256), h, frames * 2), block = 256
+__global__ void __launch_bounds__(256) bm_fill_kernel(const BmArgs a0, const BmArgs a1)
+{
+    const int view = blockIdx.z & 1, frame = blockIdx.z >> 1;
+    if (view == 1 && a1.disp == a0.disp) return;
+    const BmArgs& a = view ? a1 : a0;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= a.w || y >= a.h) return;
+    const BmPlan P = bm_plan(a.w, a.h, a.ndisp, a.wsz, a.mindisp);
+    const bool computed = P.lofs < a.w && P.rofs < a.w && P.width1 >= 1 && y >= P.y0 && y < P.y1 && x >= P.lofs && x < P.lofs + P.width1;
+    if (!computed) a.disp[(size_t)frame * a.d_frame + (size_t)y * a.d_step + x] = (int16_t)((a.mindisp - 1) * 16);
+}
+
+// views halved: out(y, x, ch) = (s(2y, 2x) + s(2y, 2x+1) + s(2y+1, 2x) + s(2y+1, 2x+1) + 2) >> 2 per channel, which is what
+// cv::resize(INTER_LINEAR) computes at scale 0.5 for even sizes.  grid = (ceil(w*cn/256), h, frames * 2), block = 256
+struct HalfArgs {
+    const uint8_t* src[2]; int64_t s_step[2], s_frame[2];
+    uint8_t* dst[2]; int64_t d_step, d_frame;
+    int w, h, cn;                                       // output size
+};
+__global__ void __launch_bounds__(256) half_kernel(const HalfArgs a)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, v = blockIdx.z & 1, frame = blockIdx.z >> 1;
+    if (k >= a.w * a.cn) return;
+    const int x = k / a.cn, ch = k - x * a.cn;
+    const uint8_t* s = a.src[v] + (size_t)frame * a.s_frame[v] + (size_t)(2 * y) * a.s_step[v] + (size_t)(2 * x) * a.cn + ch;
+    const int sum = s[0] + s[a.cn] + s[a.s_step[v]] + s[a.s_step[v] + a.cn];
+    a.dst[v][(size_t)frame * a.d_frame + (size_t)y * a.d_step + k] = (uint8_t)((sum + 2) >> 2);
+}
+
+}  // namespace dwls

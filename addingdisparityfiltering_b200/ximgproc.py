@@ -136,14 +136,22 @@ def createDisparityWLSFilter(matcher_left, ctx=None):
 
 
 def createRightMatcher(matcher_left):
-    """disparity_filters.cpp:416-449 (needs cv2 for the matcher classes, exactly like the reference needs calib3d)."""
-    import cv2
+    """disparity_filters.cpp:416-449 (needs cv2 for its matcher classes, exactly like the reference needs calib3d; the
+    device matcher addingdisparityfiltering_b200.StereoBM needs nothing)."""
+    try:
+        import cv2
+    except ImportError:
+        cv2 = None
     min_disp = matcher_left.getMinDisparity()
     num_disp = matcher_left.getNumDisparities()
     wsize = matcher_left.getBlockSize()
     kind = _matcher_kind(matcher_left)
     if kind == "bm":
-        right = cv2.StereoBM_create(num_disp, wsize)
+        from .stereo import StereoBM
+        # the device matcher gets a device right matcher (same class, same context), a cv2 matcher a cv2 one
+        right = StereoBM.create(num_disp, wsize, ctx=matcher_left._ctx) if isinstance(matcher_left, StereoBM) else cv2.StereoBM_create(num_disp, wsize)
+        if isinstance(matcher_left, StereoBM):
+            right.setPreFilterCap(matcher_left.getPreFilterCap())
         right.setMinDisparity(-(min_disp + num_disp) + 1)
         right.setTextureThreshold(0)
         right.setUniquenessRatio(0)

@@ -156,6 +156,42 @@ DWLS_API dwls_status dwls_lrc_mask_host(dwls_ctx* ctx, const dwls_image* disp_le
 DWLS_API dwls_status dwls_fgs_weights_host(dwls_ctx* ctx, const dwls_image* guide, double sigma_color,
                                            float* chor, float* cvert);
 
+/* ---- stereo block matching on the device: the producer of the filter's inputs ---------------------
+ * Replaces cv::StereoBM::compute as the reference's sample calls it (samples/disparity_filtering.cpp:148-160) for the
+ * matcher pair createDisparityWLSFilter / createRightMatcher configure (src/disparity_filters.cpp:389-403, 419-428):
+ * PREFILTER_XSOBEL with cap, SAD over a block_size^2 window, winner-takes-all, optional texture / uniqueness tests,
+ * parabola sub-pixel fit, FILTERED = (min_disparity - 1) * 16 outside the valid-disparity rectangle.  disp12MaxDiff and
+ * speckle filtering are not implemented (both factories switch them off, :389-390, :426-427).  Bit-exact CV_16S. */
+typedef struct dwls_bm_params {
+    int num_disparities;      /* positive, divisible by 16 */
+    int block_size;           /* odd, >= 5 */
+    int min_disparity;
+    int pre_filter_cap;       /* 31 */
+    int texture_threshold;    /* cv default 10; createDisparityWLSFilter sets 0 */
+    int uniqueness_ratio;     /* cv default 15; createDisparityWLSFilter sets 0 */
+} dwls_bm_params;
+
+/* a batch of stereo views on the device (frame f of an array at base + f * frame stride, bytes) */
+typedef struct dwls_views {
+    int n_frames;
+    const uint8_t* left;  int64_t left_step, left_frame;
+    const uint8_t* right; int64_t right_step, right_frame;
+    int cols, rows, channels;      /* CV_8UC1, or CV_8UC3 in BGR order (converted like cvtColor BGR2GRAY) */
+} dwls_views;
+
+DWLS_API void        dwls_bm_default_params(dwls_bm_params* p);
+/* disp_left = matcher.compute(left, right); disp_right (NULL to skip) = createRightMatcher(matcher).compute(right, left),
+ * i.e. the same matcher on swapped views with minDisparity -(min + num) + 1.  Strides in bytes.  Asynchronous on `stream`. */
+DWLS_API dwls_status dwls_stereo_bm_dev(dwls_ctx* ctx, const dwls_views* views, const dwls_bm_params* params,
+                                        int16_t* disp_left, int64_t dl_step, int64_t dl_frame,
+                                        int16_t* disp_right, int64_t dr_step, int64_t dr_frame, void* stream);
+/* same for one pair of host images; disp_right may be NULL */
+DWLS_API dwls_status dwls_stereo_bm_host(dwls_ctx* ctx, const dwls_image* left, const dwls_image* right, const dwls_bm_params* params,
+                                         dwls_image* disp_left, dwls_image* disp_right);
+/* the sample's downscale step on the device (cv::resize by 0.5 of even-sized views, samples/disparity_filtering.cpp:138-139) */
+DWLS_API dwls_status dwls_halve_views_dev(dwls_ctx* ctx, const dwls_views* views, uint8_t* left_out, uint8_t* right_out,
+                                          int64_t out_step, int64_t out_frame, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
