@@ -136,6 +136,20 @@ def shard_frames(n_frames, world_size, rank):
     return begin, begin + base + (1 if rank < rem else 0)
 
 
+def shard_frames_weighted(n_frames, world_size, rank, root=0, root_extra=0):
+    """Contiguous blocks like shard_frames, but the gather root owns `root_extra` frames more than an even share (taken
+    evenly from the other ranks).  The root's own results need no transfer, so with a few extra frames on the root the
+    other ranks finish early and the gather of their LAST chunk hides behind the root's remaining kernels."""
+    if world_size == 1 or root_extra <= 0:
+        return shard_frames(n_frames, world_size, rank)
+    extra = min(root_extra, n_frames)
+    base, rem = divmod(n_frames - extra, world_size)
+    sizes = [base + (1 if r < rem else 0) for r in range(world_size)]
+    sizes[root] += extra
+    begin = sum(sizes[:rank])
+    return begin, begin + sizes[rank]
+
+
 def gather_results(local_out, group=None):
     """all_gather of the CV_16S outputs over NCCL (GPU tensors) or gloo (CPU tensors).  Every rank must hold
     the same number of frames (pad the tail shard).  Returns [world * n_local, H, W]."""
@@ -179,7 +193,7 @@ class ShardedBatch:
     directly at their final position in `full` (frame order of the unsharded batch) - no staging copy, no reorder pass;
     a rank's own shard is a view of `full`, so the root's own results need no copy either."""
 
-    def __init__(self, n_total, frame_shape, chunk=16, tail_min=4, mode="root", dst=0, group=None, device=None, dtype=None):
+    def __init__(self, n_total, frame_shape, chunk=16, tail_min=4, mode="root", dst=0, group=None, device=None, dtype=None, root_extra=0):
         import torch
         import torch.distributed as dist
         self.dist = dist if dist.is_available() and dist.is_initialized() else None
@@ -187,7 +201,7 @@ class ShardedBatch:
         self.world = self.dist.get_world_size(group) if self.dist else 1
         self.rank = self.dist.get_rank(group) if self.dist else 0
         self.n_total, self.mode, self.dst = n_total, mode, dst
-        self.spans = [shard_frames(n_total, self.world, r) for r in range(self.world)]
+        self.spans = [shard_frames_weighted(n_total, self.world, r, dst, root_extra if mode == "root" else 0) for r in range(self.world)]
         self.begin, self.end = self.spans[self.rank]
         self.plans = [chunk_plan(e - b, chunk, tail_min) for b, e in self.spans]      # every rank can derive every peer's plan
         self.plan = self.plans[self.rank]

@@ -149,6 +149,36 @@ inline Ptr<DisparityWLSFilter> createDisparityWLSFilterGeneric(bool use_confiden
     return Ptr<DisparityWLSFilter>(new DisparityWLSFilterB200(use_confidence));
 }
 
+#if !DWLS_REAL_OPENCV
+// cv::StereoBM whose compute() runs on the GPU (dwls_stereo_bm_host): the matcher of the sample
+// (samples/disparity_filtering.cpp:148-160) with the disparities cv::StereoBM::compute returns, bit for bit.  A matcher made
+// by createRightMatcher from one of these is one of these.  (With a real OpenCV build use cv::StereoBM itself or call
+// dwls_stereo_bm_host directly: cv::StereoBM has more pure virtuals than this facade needs to restate.)
+class StereoBMB200 : public StereoBM {
+public:
+    static Ptr<StereoBMB200> create(int numDisparities = 0, int blockSize = 21)
+    {
+        Ptr<StereoBMB200> m = std::make_shared<StereoBMB200>();
+        m->numDisparities = numDisparities ? numDisparities : 64; m->blockSize = blockSize;
+        return m;
+    }
+    void compute(InputArray left_, InputArray right_, OutputArray disparity_) override
+    {
+        dwls_ctx* ctx = detail::thread_ctx();
+        const Mat left = detail::mat_of(left_), right = detail::mat_of(right_);
+        if (left.empty() || right.empty() || left.rows != right.rows || left.cols != right.cols || left.type() != right.type()) detail::check(nullptr, DWLS_BAD_ARG);
+        if (speckleWindowSize > 0 || (disp12MaxDiff >= 0 && disp12MaxDiff < 1000000)) detail::check(nullptr, DWLS_UNSUPPORTED);
+        detail::create_out(disparity_, left.rows, left.cols, CV_16SC1);
+        Mat disp = detail::out_mat(disparity_);
+        dwls_bm_params p;
+        p.num_disparities = numDisparities; p.block_size = blockSize; p.min_disparity = minDisparity; p.pre_filter_cap = preFilterCap;
+        p.texture_threshold = textureThreshold; p.uniqueness_ratio = uniquenessRatio;
+        dwls_image l = detail::image_of(left), r = detail::image_of(right), d = detail::image_of(disp);
+        detail::check(ctx, dwls_stereo_bm_host(ctx, &l, &r, &p, &d, nullptr));
+    }
+};
+#endif
+
 // src/disparity_filters.cpp:385-414 — mutates the matcher, derives ROI margins and the discontinuity radius
 inline Ptr<DisparityWLSFilter> createDisparityWLSFilter(Ptr<StereoMatcher> matcher_left)
 {
@@ -176,7 +206,12 @@ inline Ptr<StereoMatcher> createRightMatcher(Ptr<StereoMatcher> matcher_left)
 {
     const int min_disp = matcher_left->getMinDisparity(), num_disp = matcher_left->getNumDisparities(), wsize = matcher_left->getBlockSize();
     if (std::dynamic_pointer_cast<StereoBM>(matcher_left)) {
+#if !DWLS_REAL_OPENCV
+        Ptr<StereoBM> right_bm = std::dynamic_pointer_cast<StereoBMB200>(matcher_left) ? Ptr<StereoBM>(StereoBMB200::create(num_disp, wsize)) : StereoBM::create(num_disp, wsize);
+        right_bm->setPreFilterCap(std::dynamic_pointer_cast<StereoBM>(matcher_left)->getPreFilterCap());
+#else
         Ptr<StereoBM> right_bm = StereoBM::create(num_disp, wsize);
+#endif
         right_bm->setMinDisparity(-(min_disp + num_disp) + 1);
         right_bm->setTextureThreshold(0);
         right_bm->setUniquenessRatio(0);

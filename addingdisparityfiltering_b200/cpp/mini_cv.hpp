@@ -123,15 +123,17 @@ public:
     virtual int getBlockSize() const = 0;       virtual void setBlockSize(int) = 0;
     virtual int getSpeckleWindowSize() const = 0; virtual void setSpeckleWindowSize(int) = 0;
     virtual int getDisp12MaxDiff() const = 0;   virtual void setDisp12MaxDiff(int) = 0;
+    // cv::StereoMatcher::compute; the stand-in classes below only hold parameters, cv::ximgproc::StereoBMB200 computes
+    virtual void compute(InputArray, InputArray, OutputArray) { throw Exception(Error::StsNotImplemented, "this matcher stand-in holds parameters only"); }
 };
 #define DWLS_PROP(T, Name, field) T get##Name() const override { return field; } void set##Name(T v) override { field = v; }
 #define DWLS_PROP_NEW(T, Name, field) virtual T get##Name() const { return field; } virtual void set##Name(T v) { field = v; }
 class StereoBM : public StereoMatcher {
 public:
-    int minDisparity = 0, numDisparities = 64, blockSize = 21, speckleWindowSize = 0, disp12MaxDiff = -1, textureThreshold = 10, uniquenessRatio = 15;
+    int minDisparity = 0, numDisparities = 64, blockSize = 21, speckleWindowSize = 0, disp12MaxDiff = -1, textureThreshold = 10, uniquenessRatio = 15, preFilterCap = 31;
     DWLS_PROP(int, MinDisparity, minDisparity) DWLS_PROP(int, NumDisparities, numDisparities) DWLS_PROP(int, BlockSize, blockSize)
     DWLS_PROP(int, SpeckleWindowSize, speckleWindowSize) DWLS_PROP(int, Disp12MaxDiff, disp12MaxDiff)
-    DWLS_PROP_NEW(int, TextureThreshold, textureThreshold) DWLS_PROP_NEW(int, UniquenessRatio, uniquenessRatio)
+    DWLS_PROP_NEW(int, TextureThreshold, textureThreshold) DWLS_PROP_NEW(int, UniquenessRatio, uniquenessRatio) DWLS_PROP_NEW(int, PreFilterCap, preFilterCap)
     static Ptr<StereoBM> create(int numDisparities = 0, int blockSize = 21)
     {
         Ptr<StereoBM> m = std::make_shared<StereoBM>();

@@ -86,6 +86,9 @@ __device__ __forceinline__ float wls_normalise(float dc, float c)
 // grid = (min(rows_total, CTAs that fit), 1)
 // dynamic smem = HST * (1+S) * pitch floats | 2 * (4+2S) * l2pad_size(K) floats | HST mbarriers
 // ---------------------------------------------------------------------------------------------
+#ifndef DWLS_PACK16
+#define DWLS_PACK16 1      // final column pass: 64-bit stores of four CV_16S columns (0 = one 16-bit store per value, for A/B runs)
+#endif
 #ifndef DWLS_HST
 #define DWLS_HST 2
 #endif
@@ -440,12 +443,12 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
             const float lo = odd ? got : f[0][M - 1], hi = odd ? f[1][M - 1] : got;
             if (M - 1 < nrow) *(float2*)(Ob + (odd ? dplane : 0) + (size_t)(M - 1) * a.pitch) = make_float2(lo, hi);
         }
-        if (live && !PAIR) {
-            const size_t off0 = IL ? (size_t)frame * (S * a.p_frame) + (size_t)r0 * (S * a.pitch) + (size_t)(col - x) * S + x
-                                   : (size_t)frame * a.p_frame + (size_t)r0 * a.pitch + col;
-            const int opitch = IL ? S * a.pitch : a.pitch;
-            const int nrow = min(M, a.h - r0);                           // rows of this chunk inside the image (<= 0 for padding chunks)
-            if (FIN == FIN_FLOAT) {
+        if (FIN == FIN_FLOAT) {
+            if (live && !PAIR) {
+                const size_t off0 = IL ? (size_t)frame * (S * a.p_frame) + (size_t)r0 * (S * a.pitch) + (size_t)(col - x) * S + x
+                                       : (size_t)frame * a.p_frame + (size_t)r0 * a.pitch + col;
+                const int opitch = IL ? S * a.pitch : a.pitch;
+                const int nrow = min(M, a.h - r0);                       // rows of this chunk inside the image (<= 0 for padding chunks)
 #pragma unroll
                 for (int s = 0; s < S; ++s) {
                     float* O = IL ? a.out[0] + off0 + (s ^ sel) * VC : a.out[s] + off0;
@@ -457,26 +460,65 @@ __global__ void __launch_bounds__(MAXT) vsolve_kernel(const SolveArgs a, const V
                         for (int m = 0; m < M; ++m) if (m < nrow) O[m * opitch] = f[s][m];
                     }
                 }
-            } else {
-                int16_t* O = a.out16 + (size_t)frame * a.out16_frame + (size_t)r0 * a.out16_step + col;
-                if (IL && sel) {                                         // this chunk holds the planes the other way round
+            }
+        } else {
+            // fused epilogue of the last column pass: normalise (confidence path), round to CV_16S, store into the ROI of the
+            // full-size output.  Every thread runs the arithmetic and the shuffles (padding chunks and columns past the ROI
+            // hold zeros); only the stores are predicated.
+            const int nrow = min(M, a.h - r0);
+            if (IL && sel) {                                             // this chunk holds the planes the other way round
 #pragma unroll
-                    for (int m = 0; m < M; ++m) { const float q = f[0][m]; f[0][m] = f[S - 1][m]; f[S - 1][m] = q; }
+                for (int m = 0; m < M; ++m) { const float q = f[0][m]; f[0][m] = f[S - 1][m]; f[S - 1][m] = q; }
+            }
+            if (FIN == FIN_WLS) {
+                // one range test for the chunk, then straight-line code (the exact division is for denominators no
+                // confidence map produces)
+                bool huge = false;
+#pragma unroll
+                for (int m = 0; m < M; ++m) { f[S - 1][m] = wls_den(f[S - 1][m]); huge |= wls_den_huge(f[S - 1][m]); }
+                if (!huge) {
+#pragma unroll
+                    for (int m = 0; m < M; ++m) f[0][m] = __fmul_rn(f[0][m], wls_rcp_scaled(f[S - 1][m]));
+                } else {
+#pragma unroll
+                    for (int m = 0; m < M; ++m) f[0][m] = __fmul_rn(f[0][m], __fdiv_rn(1.0f, f[S - 1][m]));
                 }
-                if (FIN == FIN_WLS) {
-                    // one range test for the chunk, then straight-line code (the exact division is for denominators no
-                    // confidence map produces)
-                    bool huge = false;
+            }
+            int16_t* O = a.out16 + (size_t)frame * a.out16_frame + (size_t)r0 * a.out16_step + col;
+            // 8-column strips with an 8-byte aligned output: four neighbouring columns trade rows so that a lane stores FOUR
+            // adjacent CV_16S values of one row with one 64-bit store (two packed exchanges per 4 rows instead of 4 narrow
+            // stores per lane: the LSU queue, not the arithmetic, is what this pass waits for)
+            const bool packed = DWLS_PACK16 && VC == 8 && (((uintptr_t)a.out16 | (uintptr_t)(a.out16_step * 2) | (uintptr_t)(a.out16_frame * 2)) & 7) == 0;   // uniform
+            if (packed) {
+                const int col4 = col - (x & 3);
+                const bool grp_ok = col4 + 3 < a.w;                      // the same for the four lanes of a group
+                const bool odd = x & 1, hi = x & 2;
 #pragma unroll
-                    for (int m = 0; m < M; ++m) { f[S - 1][m] = wls_den(f[S - 1][m]); huge |= wls_den_huge(f[S - 1][m]); }
-                    if (!huge) {
-#pragma unroll
-                        for (int m = 0; m < M; ++m) f[0][m] = __fmul_rn(f[0][m], wls_rcp_scaled(f[S - 1][m]));
-                    } else {
-#pragma unroll
-                        for (int m = 0; m < M; ++m) f[0][m] = __fmul_rn(f[0][m], __fdiv_rn(1.0f, f[S - 1][m]));
+                for (int g4 = 0; g4 + 3 < M; g4 += 4) {
+                    const uint32_t r0v = (uint16_t)cvt_s16(f[0][g4]), r1v = (uint16_t)cvt_s16(f[0][g4 + 1]), r2v = (uint16_t)cvt_s16(f[0][g4 + 2]),
+                                   r3v = (uint16_t)cvt_s16(f[0][g4 + 3]);
+                    // stage 1 (lane ^ 1): even lanes collect row g4 (and g4+2) of their column pair, odd lanes row g4+1 (g4+3)
+                    const uint32_t snd01 = odd ? r0v : r1v, snd23 = odd ? r2v : r3v;
+                    const uint32_t got01 = __shfl_xor_sync(0xffffffffu, snd01, 1), got23 = __shfl_xor_sync(0xffffffffu, snd23, 1);
+                    const uint32_t w01 = odd ? (got01 | (r1v << 16)) : (r0v | (got01 << 16));
+                    const uint32_t w23 = odd ? (got23 | (r3v << 16)) : (r2v | (got23 << 16));
+                    // stage 2 (lane ^ 2): the low pair of lanes keeps rows g4 / g4+1, the high pair rows g4+2 / g4+3
+                    const uint32_t got = __shfl_xor_sync(0xffffffffu, hi ? w01 : w23, 2);
+                    const uint32_t keep = hi ? w23 : w01;
+                    const int row = g4 + (odd ? 1 : 0) + (hi ? 2 : 0);
+                    if (grp_ok) {
+                        if (row < nrow) *(uint2*)(O - (x & 3) + (size_t)row * a.out16_step) = hi ? make_uint2(got, keep) : make_uint2(keep, got);
+                    } else if (live) {
+                        if (g4 < nrow) O[(size_t)g4 * a.out16_step] = (int16_t)r0v;
+                        if (g4 + 1 < nrow) O[(size_t)(g4 + 1) * a.out16_step] = (int16_t)r1v;
+                        if (g4 + 2 < nrow) O[(size_t)(g4 + 2) * a.out16_step] = (int16_t)r2v;
+                        if (g4 + 3 < nrow) O[(size_t)(g4 + 3) * a.out16_step] = (int16_t)r3v;
                     }
                 }
+#pragma unroll
+                for (int m = M - (M & 3); m < M; ++m)
+                    if (live && m < nrow) O[(size_t)m * a.out16_step] = cvt_s16(f[0][m]);
+            } else if (live) {
                 if (nrow == M) {
 #pragma unroll
                     for (int m = 0; m < M; ++m) O[(size_t)m * a.out16_step] = cvt_s16(f[0][m]);

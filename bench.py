@@ -297,6 +297,7 @@ def main():
     ap.add_argument("--chunk", type=int, default=0, help="frames per launch / gather chunk (0 = 32 on one GPU, 16 on several)")
     ap.add_argument("--tail-min", type=int, default=-1, help="smallest halved tail chunk (-1 = 0 on one GPU, 4 on several)")
     ap.add_argument("--gather-mode", default="root", choices=["root", "all"])
+    ap.add_argument("--root-extra", type=int, default=0, help="frames the gather root owns beyond an even share (its results need no transfer)")
     ap.add_argument("--group", type=int, default=0, help="frames per kernel launch group inside a chunk (0 = library default)")
     ap.add_argument("--lanes", type=int, default=0, help="internal streams the launch groups of a chunk are dealt to (0 = library default)")
     ap.add_argument("--e2e-frames", type=int, default=64, help="frames per rank and step of the end-to-end (host buffer) leg")
@@ -343,7 +344,7 @@ def main():
         for fr in tb:
             for t in fr:
                 dist.broadcast(t.view(torch.uint8), src=0)
-    sb = ShardedBatch(args.frames, (H, W), chunk=chunk, tail_min=tail_min, mode=args.gather_mode, dst=0, device=dev)
+    sb = ShardedBatch(args.frames, (H, W), chunk=chunk, tail_min=tail_min, mode=args.gather_mode, dst=0, device=dev, root_extra=args.root_extra)
     nloc = sb.end - sb.begin
 
     def build(k):          # frame f of the batch = base frame f % N_BASE rolled by 3 f columns (left / right / view alike)

@@ -62,6 +62,27 @@ int main(int argc, char** argv)
     fastGlobalSmootherFilter(view, src, fgs, lambda, sigma);
     save(dir + "/fgs.bin", fgs);
 
+    // 3b. the device matcher in place of cv::StereoBM: the sample's matching step (samples/disparity_filtering.cpp:148-160)
+    //     on <dir>/gl.bin, gr.bin (8UC1, dw x dh) when present -> bm_l.bin, bm_r.bin, bm_out.bin
+    {
+        FILE* probe = fopen((dir + "/gl.bin").c_str(), "rb");
+        if (probe) {
+            fclose(probe);
+            Mat gl(dh, dw, CV_8UC1), gr(dh, dw, CV_8UC1), bl, br, fout;
+            load(dir + "/gl.bin", gl); load(dir + "/gr.bin", gr);
+            Ptr<StereoBMB200> lm = StereoBMB200::create(48, 7);
+            Ptr<DisparityWLSFilter> w3 = createDisparityWLSFilter(lm);
+            Ptr<StereoMatcher> rm = createRightMatcher(lm);
+            lm->compute(gl, gr, bl);
+            rm->compute(gr, gl, br);
+            w3->setLambda(lambda); w3->setSigmaColor(sigma);
+            w3->filter(bl, view, fout, br);
+            Rect q = w3->getROI();
+            printf("ROI3 %d %d %d %d\n", q.x, q.y, q.width, q.height);
+            save(dir + "/bm_l.bin", bl); save(dir + "/bm_r.bin", br); save(dir + "/bm_out.bin", fout);
+        }
+    }
+
     // 4. error behaviour: exceptions like CV_Assert / CV_Error(StsBadSize)
     int caught = 0;
     try { Mat bad(dh, dw, CV_32FC1), o; wls->filter(bad, view, o, dr, roi); } catch (const cv::Exception&) { caught |= 1; }

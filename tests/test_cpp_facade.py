@@ -32,7 +32,10 @@ def test_facade_matches_oracle(tmp_path):
     w, h, cn = 320, 240, 3
     view, dl, dr, roi = synth.make_artificial_example(w, h, cn, seed=21)
     src = (np.random.default_rng(1).random((h, w)) * 255).astype(np.float32)
-    for name, a in (("dl", dl), ("dr", dr), ("view", view), ("src", src)):
+    import cv2
+    left, right, _ = synth.make_stereo_pair(w, h, seed=5, bg_disp=6, min_disp=10, max_disp=40)
+    gl, gr = cv2.cvtColor(left, cv2.COLOR_BGR2GRAY), cv2.cvtColor(right, cv2.COLOR_BGR2GRAY)
+    for name, a in (("dl", dl), ("dr", dr), ("view", view), ("src", src), ("gl", gl), ("gr", gr)):
         a.tofile(str(tmp_path / (name + ".bin")))
     lam, sigma, radius = 8000.0, 1.5, 3
     res = subprocess.run([exe, str(tmp_path), str(w), str(h), str(w), str(h), str(cn)] + [str(v) for v in roi] + [str(radius), str(lam), str(sigma)],
@@ -50,6 +53,18 @@ def test_facade_matches_oracle(tmp_path):
     assert_s16_parity(out, ref["out"], roi)
     assert np.abs(conf - ref["conf"]).max() <= 1e-4
     assert np.abs(fgs - O.fgs_filter(view, src, lam, sigma)).max() <= 255 * 1e-3
+    # the device matcher through the C++ facade == cv2.StereoBM, and its filtered map == the oracle on cv2's maps
+    import addingdisparityfiltering_b200 as A
+    lm = cv2.StereoBM_create(48, 7)
+    f = A.createDisparityWLSFilter(lm)
+    rm = A.createRightMatcher(lm)
+    want_l, want_r = lm.compute(gl, gr), rm.compute(gr, gl)
+    bm_l = np.fromfile(str(tmp_path / "bm_l.bin"), np.int16).reshape(h, w)
+    bm_r = np.fromfile(str(tmp_path / "bm_r.bin"), np.int16).reshape(h, w)
+    assert (bm_l == want_l).all() and (bm_r == want_r).all()
+    ref3 = O.wls_filter(want_l, view, want_r, lam=lam, sigma=sigma, disc_radius=f.getDepthDiscontinuityRadius(), offsets=f._offsets)
+    assert tuple(int(v) for v in lines["ROI3"]) == ref3["roi"]
+    assert_s16_parity(np.fromfile(str(tmp_path / "bm_out.bin"), np.int16).reshape(h, w), ref3["out"], ref3["roi"])
 
 
 def test_quality_helpers_match_the_reference_bit_for_bit(tmp_path):
