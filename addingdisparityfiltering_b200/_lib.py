@@ -63,8 +63,14 @@ def build(force=False, verbose=False):
     srcs.append(os.path.join(_HERE, "..", "include", "dwls_b200.h"))
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(s) <= os.path.getmtime(LIB_PATH) for s in srcs):
         return LIB_PATH
-    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH, os.path.join(CSRC, "dwls_capi.cu")]
-    subprocess.check_call(cmd)
+    tmp = LIB_PATH + ".build%d.so" % os.getpid()        # build beside the target, then rename: a reader never sees a half-written library
+    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", tmp, os.path.join(CSRC, "dwls_capi.cu")]
+    try:
+        subprocess.check_call(cmd)
+        os.replace(tmp, LIB_PATH)
+    finally:
+        if os.path.exists(tmp):
+            os.remove(tmp)
     return LIB_PATH
 
 
