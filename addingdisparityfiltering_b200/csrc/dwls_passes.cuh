@@ -87,7 +87,12 @@ __device__ __forceinline__ float wls_normalise(float dc, float c)
 // dynamic smem = HST * (1+S) * pitch floats | 2 * (4+2S) * l2pad_size(K) floats | HST mbarriers
 // ---------------------------------------------------------------------------------------------
 #ifndef DWLS_PACK16
-#define DWLS_PACK16 1      // final column pass: 64-bit stores of four CV_16S columns (0 = one 16-bit store per value, for A/B runs)
+#define DWLS_PACK16 0      // final column pass: 1 = four columns trade rows and a lane stores 4 CV_16S values with one 64-bit store.
+                           // Measured (round 2, 1080p): 7.26 us / frame with it, 7.15 without - the pass is bound by its TMA tile
+                           // loads (32-byte box rows), not by its stores - so it stays off; kept for A/B runs.
+#endif
+#ifndef DWLS_H16MINB
+#define DWLS_H16MINB 2     // CTAs per SM the 16-elements-per-thread row pass (rows of 2049..4096 pixels) is compiled for
 #endif
 #ifndef DWLS_HST
 #define DWLS_HST 2
@@ -109,7 +114,7 @@ __host__ __device__ inline size_t hsolve_smem_bytes(int K, int pitch)
 }
 
 template <int S, int MAXT, int HM, bool IL = false>
-__global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : 2) : 1)) hsolve_kernel(const SolveArgs a, const int rows_total)
+__global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : DWLS_H16MINB) : 1)) hsolve_kernel(const SolveArgs a, const int rows_total)
 {
     extern __shared__ __align__(128) float sm[];
     const int K = blockDim.x, M2 = K >> 5, KP = l2pad_size(K);

@@ -154,7 +154,13 @@ def cpu_frames_per_sec(base, n_frames, threads):
 
 
 def default_chunk(world):
-    return 32 if world == 1 else 16
+    """Frames per launch / gather chunk: 32-frame launches are the most efficient ones (one rank, or two ranks with 256 frames
+    each); with 128 or 64 frames per rank the chunks shrink to 16 so that the gather starts early and its exposed tail is short."""
+    return 32 if world <= 2 else 16
+
+
+def default_tail(world):
+    return 0 if world == 1 else (8 if world == 2 else 4)
 
 
 def base_config(frames_total, world, source, chunk=0):
@@ -294,8 +300,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--frames", type=int, default=512, help="frames of the whole batch per step (sharded over the GPUs)")
-    ap.add_argument("--chunk", type=int, default=0, help="frames per launch / gather chunk (0 = 32 on one GPU, 16 on several)")
-    ap.add_argument("--tail-min", type=int, default=-1, help="smallest halved tail chunk (-1 = 0 on one GPU, 4 on several)")
+    ap.add_argument("--chunk", type=int, default=0, help="frames per launch / gather chunk (0 = 32 on one or two GPUs, 16 on more)")
+    ap.add_argument("--tail-min", type=int, default=-1, help="smallest halved tail chunk (-1 = none on one GPU, 8 on two, 4 on more)")
     ap.add_argument("--gather-mode", default="root", choices=["root", "all"])
     ap.add_argument("--root-extra", type=int, default=0, help="frames the gather root owns beyond an even share (its results need no transfer)")
     ap.add_argument("--group", type=int, default=0, help="frames per kernel launch group inside a chunk (0 = library default)")
@@ -330,7 +336,7 @@ def main():
     if args.lanes:
         ctx.set_lanes(args.lanes)
     chunk = args.chunk or default_chunk(world)
-    tail_min = args.tail_min if args.tail_min >= 0 else (0 if world == 1 else 4)
+    tail_min = args.tail_min if args.tail_min >= 0 else default_tail(world)
 
     # ---- inputs: rank 0 runs the stereo matcher, the other ranks receive the base frames over NCCL ----
     if rank == 0:
