@@ -1,20 +1,16 @@
 #!/bin/bash
 # the job the next gpurun call executes (edited between calls; gpurun snapshots the tree when the call starts)
-set -x
+echo "== single call, small-launch grid shapes on / off"
 python tools/single_kernels.py 1
 DWLS_SMALL_GRIDS=0 python tools/single_kernels.py 1
-python tools/single_kernels.py 2
-python - <<'PY'
-import json, subprocess, os, sys
-# configs[2] FGS 4K with the default library and the 3-CTAs-per-SM row pass variant
-for lib in ("", "exp/variants/libdwls_h16x3.so"):
-    env = dict(os.environ)
-    if lib: env["DWLS_LIB"] = lib
-    out = subprocess.run([sys.executable, "tools/bench_configs.py"], capture_output=True, text=True, env=env).stdout
-    try:
-        d = json.loads(out[out.index("{"):])
-        print(lib or "default", {k: (v.get("ms_per_call"), v.get("kernels_us_per_call")) for k, v in d.items() if "fgs" in k})
-    except Exception as e:
-        print("failed", lib, e, out[-500:])
-PY
-python tools/cpu_configs.py
+echo "== bench, default flags"
+python bench.py > gpurun_out/bench_r02_n1.json 2> gpurun_out/bench_r02_n1.err; tail -c 1500 gpurun_out/bench_r02_n1.json; tail -3 gpurun_out/bench_r02_n1.err
+python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_r02_ref.json 2>&1
+echo "== ncu"
+CMD="python bench.py --frames 32 --steps 2 --warmup 1 --no-cpu --no-e2e --no-extras"
+$CMD > gpurun_out/plain.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches_r02.csv $CMD > gpurun_out/ncu_list.log 2>&1
+$CMD > gpurun_out/plain2.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k "regex:conf_run|weights_k|solve_k|border_k" -s 10 -c 10 -f -o gpurun_out/full_r02 $CMD > gpurun_out/ncu_full.log 2>&1
+tail -3 gpurun_out/ncu_full.log
+ls -la gpurun_out/ | tail -8
