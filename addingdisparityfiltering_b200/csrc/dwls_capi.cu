@@ -177,12 +177,6 @@ struct KTimer {
 
 static std::string g_create_err;
 
-// launch-shape heuristics for launches that cannot fill the GPU (DWLS_SMALL_GRIDS=0 switches them off for A/B runs)
-static bool small_grids()
-{
-    static const bool on = [] { const char* e = getenv("DWLS_SMALL_GRIDS"); return !(e && e[0] == '0'); }();
-    return on;
-}
 
 #define CK(call)                                                                                     \
     do {                                                                                             \
@@ -598,13 +592,9 @@ static dwls_status launch_weights(dwls_ctx* ctx, const uint8_t* guide, int64_t g
                                   int pitch, float* chor, float* cvert, int64_t wframe, int frames, cudaStream_t st, int vstrip)
 {
     if (vstrip <= 0) vstrip = pitch;
-    // threads per CTA: spread the row over equally wide tiles of at most 1024 pixels; a launch too small to fill the
-    // machine (single frames) gets narrower tiles: about four CTAs per SM instead of two half-empty ones
-    int tiles = (pitch + 1023) / 1024;
-    if (small_grids()) {
-        const int rows_y = (h + WT_RB - 1) / WT_RB;
-        while (tiles < 8 && (int64_t)tiles * rows_y * frames < 4LL * ctx->num_sms && pitch / (tiles * 2) >= 128) tiles *= 2;
-    }
+    // threads per CTA: spread the row over equally wide tiles of at most 1024 pixels.  (Narrower tiles for launches too small
+    // to fill the machine were measured in round 2 and lose: one 1080p frame 12.9 -> 14.8 us, the conf kernels 33 -> 59 us.)
+    const int tiles = (pitch + 1023) / 1024;
     const int nt = round_up((pitch + 4 * tiles - 1) / (4 * tiles), 32);
     const int rowpitch = weights_row_pitch(nt, cn);
     const size_t smem = (size_t)(WT_RB + 1) * rowpitch + sizeof(float) * WT_LUT + 8;
@@ -666,14 +656,7 @@ static void launch_conf_run(dwls_ctx* ctx, const ConfArgs& a, int G, dim3 grid, 
 static dwls_status launch_conf(dwls_ctx* ctx, const ConfArgs& a, int frames, cudaStream_t st)
 {
     if (a.radius <= CR_MAXR) {
-        const int runs = (a.rw + 7) / 8;
-        int gmax = CR_GMAX;
-        if (small_grids()) {
-            // a launch too small to fill the machine (single frames): narrower tiles, about four CTAs per SM
-            const int rows_y = (a.rh + CR_TH - 1) / CR_TH;
-            const int64_t want_x = (4LL * ctx->num_sms + (int64_t)rows_y * frames - 1) / ((int64_t)rows_y * frames);
-            if (want_x > (runs + gmax - 1) / gmax) gmax = std::max(6, (int)((runs + want_x - 1) / want_x));
-        }
+        const int runs = (a.rw + 7) / 8, gmax = CR_GMAX;
         const int tiles = (runs + gmax - 1) / gmax, G = (runs + tiles - 1) / tiles;
         const dim3 grid(tiles, (a.rh + CR_TH - 1) / CR_TH, frames);
         const int box_rows = CR_TH + 2 * a.radius + 1;
