@@ -244,6 +244,67 @@ def extras_single_gpu(torch, A, ctx, dev, base, peak):
                           "what": "one 1080p frame per call: dwls_filter_batch_dev with n_frames=1 on device buffers (graph replay), and "
                                   "dwls_filter_host on pageable numpy arrays incl. the confidence map (what wls->filter(cv::Mat...) calls)"}
     other = {}
+    # ---- the device matcher feeding the filter (sample default path at 1080p: views halved, StereoBM(80, 7) left + right
+    #      maps, filtered at full resolution; samples/disparity_filtering.cpp:135-190), everything born in HBM ----
+    try:
+        from addingdisparityfiltering_b200.stereo import halve_views_device
+        B = 32
+        pairs = [synth.make_stereo_pair(W, H, seed=60 + i) for i in range(2)]
+        tl2 = torch.stack([torch.from_numpy(pairs[f % 2][0]).to(dev) for f in range(B)]).contiguous()
+        tr2 = torch.stack([torch.from_numpy(pairs[f % 2][1]).to(dev) for f in range(B)]).contiguous()
+        bm = A.StereoBM.create(80, 7, ctx=ctx)
+        wls = A.createDisparityWLSFilter(bm, ctx=ctx)             # margins (83,3,3,3), radius 3; switches the matcher's post-filters off
+        bfm = BatchFilter(True, LAMBDA, SIGMA, wls.getLRCthresh(), wls.getDepthDiscontinuityRadius(), offsets=wls._offsets, ctx=ctx)
+        mdl = torch.empty((B, H // 2, W // 2), dtype=torch.int16, device=dev)
+        mdr = torch.empty_like(mdl)
+        mo = torch.empty((B, H, W), dtype=torch.int16, device=dev)
+        mc = torch.empty((B, H, W), dtype=torch.float32, device=dev)
+
+        def match_and_filter():
+            hl, hr = halve_views_device(tl2, tr2, ctx=ctx)
+            bm.compute_device(hl, hr, mdl, mdr)
+            bfm.filter_device(mdl, tl2, mo, mdr, mc)
+        ms_all = cuda_time(torch, match_and_filter, 5, 2)
+        ms_match = cuda_time(torch, lambda: bm.compute_device(*halve_views_device(tl2, tr2, ctx=ctx), mdl, mdr), 5, 2)
+        t0 = time.perf_counter()
+        import cv2
+        cm = cv2.StereoBM_create(80, 7)
+        A.createDisparityWLSFilter(cm)
+        g0, g1 = (cv2.cvtColor(cv2.resize(pairs[0][k], None, fx=0.5, fy=0.5), cv2.COLOR_BGR2GRAY) for k in range(2))
+        t0 = time.perf_counter()
+        want_l = cm.compute(g0, g1)
+        want_r = A.createRightMatcher(cm).compute(g1, g0)
+        cv_ms = (time.perf_counter() - t0) * 1e3
+        assert (mdl[0].cpu().numpy() == want_l).all() and (mdr[0].cpu().numpy() == want_r).all(), "device matcher differs from cv2.StereoBM"
+        res["match_and_filter"] = {
+            "what": "sample default path at 1080p on device-resident views, 32 frames per call: halve both views, StereoBM(80,7) left + right "
+                    "matcher (bit-equal to cv2.StereoBM, checked here on frame 0), confidence-aware filter at full resolution",
+            "us_per_frame": round(ms_all * 1e3 / B, 2), "Mpix_per_s": round(B * W * H / ms_all / 1e3, 1),
+            "matching_us_per_frame": round(ms_match * 1e3 / B, 2), "cv2_StereoBM_both_maps_ms_per_frame_host": round(cv_ms, 2)}
+        del tl2, tr2, mdl, mdr, mo, mc
+    except ImportError:
+        pass
+    # ---- configs[0]: 640x480 sample default (320x240 StereoBM maps, ROI (83,3,234,234), r=3), 128 frames ----
+    try:
+        import cv2
+        from tests.stereo_inputs import sample_matching
+        B = 128
+        l0, r0, _ = synth.make_stereo_pair(640, 480, seed=42, max_disp=140)
+        f0, d0l, d0r = sample_matching(l0, r0, "bm", downscale=True, max_disp=160, ctx=ctx)
+        sv = torch.from_numpy(l0).to(dev).expand(B, -1, -1, -1).contiguous()
+        sl = torch.from_numpy(d0l).to(dev).expand(B, -1, -1).contiguous()
+        sr = torch.from_numpy(d0r).to(dev).expand(B, -1, -1).contiguous()
+        so = torch.empty((B, 480, 640), dtype=torch.int16, device=dev)
+        sc = torch.empty((B, 480, 640), dtype=torch.float32, device=dev)
+        bf0 = BatchFilter(True, LAMBDA, SIGMA, f0.getLRCthresh(), f0.getDepthDiscontinuityRadius(), offsets=f0._offsets, ctx=ctx)
+        ms = cuda_time(torch, lambda: bf0.filter_device(sl, sv, so, sr, sc), 5, 2)
+        N0, n0, fd0, F0 = 468 * 468, 234 * 234, 320 * 240, 640 * 480
+        alg0 = 14 * n0 + 4 * fd0 + 6 * fd0 + 6 * F0 + 14 * N0 + (CN + 8) * N0 + 6 * (4 * N0 + 16 * N0) - 8 * N0 + 2 * F0
+        other["configs[0] 640x480 StereoBM sample default (320x240 maps, ROI (83,3,234,234), r=3), 128 frames"] = {
+            "Mpix_per_s": round(B * F0 / ms / 1e3, 1), "us_per_frame": round(ms * 1e3 / B, 2), "alg_roofline_frac": round(alg0 * B / (ms * 1e-3) / 1e9 / peak, 3)}
+        del sv, sl, sr, so, sc
+    except ImportError:
+        pass
     # ---- configs[3]: half resolution, 32 frames ----
     try:
         import cv2
