@@ -51,6 +51,7 @@ class Batch(C.Structure):
 EXPORTS = ["dwls_default_params", "dwls_ctx_create", "dwls_ctx_destroy", "dwls_last_error", "dwls_version",
            "dwls_kernel_launches", "dwls_set_group_frames", "dwls_set_lanes", "dwls_set_kernel_timing", "dwls_kernel_timing_report", "dwls_set_cuda_graphs", "dwls_set_plane_interleave", "dwls_graph_replays", "dwls_transfer_bytes", "dwls_filter_host", "dwls_filter_batch_dev",
            "dwls_filter_batch_host", "dwls_fgs_host", "dwls_fgs_dev", "dwls_lrc_mask_host", "dwls_fgs_weights_host",
+           "dwls_fgs_dev_noalloc", "dwls_fgs_noalloc_scratch_bytes", "dwls_fgs_noalloc_required_bytes",
            "dwls_bm_default_params", "dwls_stereo_bm_dev", "dwls_stereo_bm_host", "dwls_halve_views_dev"]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -1624,3 +1624,112 @@ extern "C" dwls_status dwls_halve_views_dev(dwls_ctx* ctx, const dwls_views* v, 
     CK(call_leave(ctx, st));
     return DWLS_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// fastGlobalSmootherFilter on device buffers WITHOUT any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA-graph capture, tight serving
+// loops, harnesses that forbid it).  Same kernels as dwls_fgs_dev; what that entry point keeps in cudaMalloc'ed memory
+// (weight LUT, Chor, Cvert, up to 4 solver planes) lives here in ONE file-scope device array of a fixed, modest size.
+// Every GPU that loads the library holds the array until the process exits.  All calls share it and it keeps the last
+// call's contents: the plane region a call uses is cleared first, the LUT is rebuilt every call, and two calls that
+// overlap on the GPU (different streams, no ordering between them) race on it - that is the caller's to prevent.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_scratch[DWLS_NOALLOC_SCRATCH_BYTES];
+
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: its device address is fetched once per
+// device, with that device current, and that pointer is what the kernels get.
+static std::mutex g_noalloc_mutex;
+static unsigned char* g_noalloc_ptr[64] = {};
+
+static dwls_status noalloc_scratch(dwls_ctx* ctx, unsigned char** out)
+{
+    if (ctx->device < 0 || ctx->device >= 64) return fail(ctx, DWLS_UNSUPPORTED, "device index beyond the no-allocation scratch table");
+    std::lock_guard<std::mutex> lk(g_noalloc_mutex);
+    if (!g_noalloc_ptr[ctx->device]) {
+        void* p = nullptr;
+        CK(cudaSetDevice(ctx->device));
+        CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) return fail(ctx, DWLS_CUDA_ERROR, "cudaGetSymbolAddress returned a null scratch address");
+        g_noalloc_ptr[ctx->device] = (unsigned char*)p;
+    }
+    *out = g_noalloc_ptr[ctx->device];
+    return DWLS_OK;
+}
+
+extern "C" size_t dwls_fgs_noalloc_scratch_bytes(void) { return (size_t)DWLS_NOALLOC_SCRATCH_BYTES; }
+
+// bytes of the static scratch a call on a w x h guide with `channels` source channels needs (0: not supported at all)
+extern "C" size_t dwls_fgs_noalloc_required_bytes(int cols, int rows, int channels)
+{
+    if (cols <= 0 || rows <= 0 || channels < 1 || channels > 4) return 0;
+    const size_t plane = (size_t)round_up(cols, 8) * rows;
+    return align256(sizeof(float) * LUT_LEVELS) + (2 + (size_t)channels) * plane * sizeof(float);
+}
+
+extern "C" dwls_status dwls_fgs_dev_noalloc(dwls_ctx* ctx, const dwls_image* guide, const dwls_image* src, dwls_image* dst, double lambda,
+                                            double sigma, double att, int num_iter, void* stream)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    dwls_status s = fgs_check(ctx, guide, src, dst, lambda, sigma, num_iter);
+    if (s) return s;
+    if (ctx->timing) return fail(ctx, DWLS_UNSUPPORTED, "dwls_fgs_dev_noalloc: per-kernel timing creates CUDA events; switch it off for this entry point");
+    const int w = guide->cols, h = guide->rows, pitch = round_up(w, 8), S = src->channels;
+    SolvePlan pl;
+    if (!plan_solver(w, h, &pl) || pl.vT)
+        return fail(ctx, DWLS_UNSUPPORTED, "dwls_fgs_dev_noalloc: images of more than 8192 columns or 2176 rows need scratch planes this entry point does not have");
+    const size_t need = dwls_fgs_noalloc_required_bytes(w, h, S);
+    if (need > (size_t)DWLS_NOALLOC_SCRATCH_BYTES) {
+        char b_[256];
+        snprintf(b_, sizeof b_, "dwls_fgs_dev_noalloc: a %d x %d image with %d channel(s) needs %zu bytes of scratch, the static array holds %zu "
+                                "(use dwls_fgs_dev, which allocates)", w, h, S, need, (size_t)DWLS_NOALLOC_SCRATCH_BYTES);
+        ctx->err = b_;
+        return DWLS_UNSUPPORTED;
+    }
+    CK(cudaSetDevice(ctx->device));
+    unsigned char* base = nullptr;
+    if ((s = noalloc_scratch(ctx, &base))) return s;
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    const size_t plane = (size_t)pitch * h;
+    float* lut = (float*)base;
+    float* chor = (float*)(base + align256(sizeof(float) * LUT_LEVELS));
+    float* cvert = chor + plane;
+    float* planes = cvert + plane;
+    // the array keeps what the last call left there: start the weight and solver planes of this call from zero
+    CK(cudaMemsetAsync(chor, 0, (2 + (size_t)S) * plane * sizeof(float), st));
+    lut_kernel<<<(LUT_LEVELS + 255) / 256, 256, 0, st>>>(lut, LUT_LEVELS, (float)sigma);
+    CK(cudaGetLastError());
+    ctx->launches++;
+    // launch_weights reads the LUT pointer from the context: point it at the scratch LUT for the duration of this call
+    // (host-side state only; the context's own LUT in device memory is neither touched nor freed)
+    struct LutSwap {
+        dwls_ctx* c; float* saved;
+        LutSwap(dwls_ctx* ctx_, float* l) : c(ctx_), saved(ctx_->lut) { c->lut = l; }
+        ~LutSwap() { c->lut = saved; }
+    } swap_(ctx, lut);
+    if ((s = launch_weights(ctx, (const uint8_t*)guide->data, guide->step, 0, guide->channels, w, h, pitch, chor, cvert, plane, 1, st, pl.wstrip))) return s;
+    const bool direct = S == 1 && src->depth == DWLS_32F && pitch == w && src->step == (int64_t)w * 4 && dst->step == (int64_t)w * 4 &&
+                        (((uintptr_t)src->data | (uintptr_t)dst->data) & 31) == 0;
+    if (!direct) {
+        if (src->depth == DWLS_8U) launch_unpack<uint8_t>(src, planes, plane, pitch, st);
+        else if (src->depth == DWLS_16S) launch_unpack<int16_t>(src, planes, plane, pitch, st);
+        else launch_unpack<float>(src, planes, plane, pitch, st);
+        CK(cudaGetLastError());
+        ctx->launches++;
+    }
+    for (int c0 = 0; c0 < S; c0 += 2) {
+        const int ns = (S - c0 >= 2) ? 2 : 1;
+        SolveArgs a;
+        memset(&a, 0, sizeof a);
+        a.w_frame = plane; a.p_frame = plane; a.pitch = pitch; a.w = w; a.h = h;
+        for (int k = 0; k < ns; ++k) { a.in[k] = planes + (size_t)(c0 + k) * plane; a.out[k] = planes + (size_t)(c0 + k) * plane; }
+        if (direct) { a.in[0] = (const float*)src->data; a.out[0] = (float*)dst->data; }
+        if ((s = run_sweeps(ctx, a, chor, cvert, ns, FIN_FLOAT, pl, 1, lambda, att, num_iter, st, nullptr))) return s;
+    }
+    if (direct) return DWLS_OK;
+    if (dst->depth == DWLS_8U) launch_pack<uint8_t>(planes, plane, pitch, dst, st);
+    else if (dst->depth == DWLS_16S) launch_pack<int16_t>(planes, plane, pitch, dst, st);
+    else launch_pack<float>(planes, plane, pitch, dst, st);
+    CK(cudaGetLastError());
+    ctx->launches++;
+    return DWLS_OK;
+}

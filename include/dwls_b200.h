@@ -24,6 +24,7 @@
 #ifndef DWLS_B200_H
 #define DWLS_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -145,6 +146,25 @@ DWLS_API dwls_status dwls_fgs_host(dwls_ctx* ctx, const dwls_image* guide, const
 DWLS_API dwls_status dwls_fgs_dev(dwls_ctx* ctx, const dwls_image* guide, const dwls_image* src, dwls_image* dst,
                                   double lambda, double sigma_color, double lambda_attenuation, int num_iter,
                                   void* stream);
+
+/* ---- fastGlobalSmootherFilter on device buffers WITHOUT any allocation -------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same arguments, kernels and results as
+ * dwls_fgs_dev, but the weight LUT, the two weight planes and the solver planes live in ONE static device array of
+ * DWLS_NOALLOC_SCRATCH_BYTES (16 MiB) inside the library - every GPU that loads the library holds it until the process
+ * exits - and the call makes no cudaMalloc / cudaFree / event or stream creation.
+ * Limit: 786432 + (2 + channels) * round_up(cols, 8) * rows * 4 bytes must fit (dwls_fgs_noalloc_required_bytes; e.g. CV_32FC1
+ * up to 1280 x 720, 8UC3 up to 960 x 540), at most 2176 rows; larger images return DWLS_UNSUPPORTED with the sizes in
+ * dwls_last_error.  Per-kernel timing must be off.
+ * All calls (of all contexts on a device) share the array, which keeps the last call's contents: each call clears the plane
+ * region it uses and rebuilds the LUT, so calls issued one after another on a stream - or ordered by events - are
+ * independent; calls that OVERLAP on the GPU race on the array and give undefined results. */
+#define DWLS_NOALLOC_SCRATCH_BYTES (16u << 20)
+DWLS_API dwls_status dwls_fgs_dev_noalloc(dwls_ctx* ctx, const dwls_image* guide, const dwls_image* src, dwls_image* dst,
+                                          double lambda, double sigma_color, double lambda_attenuation, int num_iter,
+                                          void* stream);
+DWLS_API size_t      dwls_fgs_noalloc_scratch_bytes(void);
+DWLS_API size_t      dwls_fgs_noalloc_required_bytes(int cols, int rows, int channels);
 
 /* ---- parity / debug exports ------------------------------------------------------------------
  * LRC decision per disparity pixel: 0 outside the ROI, 1 right index outside the right ROI
