@@ -1,5 +1,13 @@
 #!/bin/bash
-# the job the next gpurun call executes: 2 GPUs - NCCL correctness test, gather variants at N = 2
-python -m pytest tests/test_sharded.py -m gpu -x -q 2>&1 | tail -3
-tools/scale_variants.sh 2 "32 8 0" "32 8 0 NCCL_P2P_USE_CUDA_MEMCPY=1" "32 0 0" "16 4 0" "32 8 4"
-grep -v "^\*\|OMP_NUM\|^$" gpurun_out/b2_1.err | tail -5
+# 8 GPUs: the sharded 512-frame batch with the NCCL gather inside the timed region, a few chunk plans; then N = 4
+N=${1:-8}
+tools/scale_variants.sh $N "16 4 0" "32 0 0" "16 4 8" "8 2 0"
+grep -v "^\*\|OMP_NUM\|^$" gpurun_out/b${N}_0.err | tail -3
+# the driver's own command line for this N (default flags), kept as the profile record
+python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29777 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_r02_n$N.json 2> gpurun_out/bench_r02_n$N.err
+python - "gpurun_out/bench_r02_n$N.json" <<'PY'
+import json,sys
+for l in open(sys.argv[1]):
+    if l.startswith('{'):
+        d=json.loads(l); print("DEFAULT", d["n_gpus"], "value", round(d["value"]), "compute_only", round(d["compute_only"]["value"]), "e2e", round(d["e2e"]["value"]), round(d["e2e"]["with_confidence_map"]["value"]), "gather_in_timed_region", d["gather_in_timed_region"], d["run"]["chunk_plan_rank0"])
+PY
