@@ -137,15 +137,22 @@ def shard_frames(n_frames, world_size, rank):
 
 
 def shard_frames_weighted(n_frames, world_size, rank, root=0, root_extra=0):
-    """Contiguous blocks like shard_frames, but the gather root owns `root_extra` frames more than an even share (taken
-    evenly from the other ranks).  The root's own results need no transfer, so with a few extra frames on the root the
-    other ranks finish early and the gather of their LAST chunk hides behind the root's remaining kernels."""
-    if world_size == 1 or root_extra <= 0:
+    """Contiguous blocks like shard_frames, but the gather root owns `root_extra` frames more (> 0) or fewer (< 0) than an
+    even share; the other ranks split the rest evenly.  Fewer is the useful direction when many ranks send to one root: the
+    root's own results need no transfer, but while it computes it also receives everybody else's (the receive kernels take SMs
+    and HBM bandwidth from a bandwidth-bound filter), so it should finish its own, smaller block together with the others."""
+    if world_size == 1 or root_extra == 0:
         return shard_frames(n_frames, world_size, rank)
-    extra = min(root_extra, n_frames)
-    base, rem = divmod(n_frames - extra, world_size)
-    sizes = [base + (1 if r < rem else 0) for r in range(world_size)]
-    sizes[root] += extra
+    even = n_frames // world_size
+    root_size = max(0, min(n_frames, even + root_extra))
+    base, rem = divmod(n_frames - root_size, world_size - 1)
+    sizes, j = [], 0
+    for r in range(world_size):
+        if r == root:
+            sizes.append(root_size)
+        else:
+            sizes.append(base + (1 if j < rem else 0))
+            j += 1
     begin = sum(sizes[:rank])
     return begin, begin + sizes[rank]
 

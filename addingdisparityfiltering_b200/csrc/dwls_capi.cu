@@ -1449,15 +1449,18 @@ extern "C" dwls_status dwls_filter_batch_host(dwls_ctx* ctx, const dwls_batch* h
             // upload only what the filter reads (the windows are whole frames when the ROI is the whole image)
             dwls_status cs;
             int x0, x1, y0, y1;
+            // DWLS_E2E_WINDOWS=0 (A/B runs): whole frames in one contiguous copy each instead of the ROI column windows
+            static const bool windows = [] { const char* e = getenv("DWLS_E2E_WINDOWS"); return !(e && e[0] == '0'); }();
+            const int wmargin = windows ? 8 : (1 << 20);
             read_window(g.ry, g.rh, dh, 8, 1, &y0, &y1);
             if (y1 - y0 != dh) { y0 = 0; y1 = dh; }           // row windows would split the batch into one copy per frame: not worth it
-            read_window(g.rx, g.rw, dw, 8, 32, &x0, &x1);
+            read_window(g.rx, g.rw, dw, wmargin, 32, &x0, &x1);
             if ((cs = copy_frames(ctx, d_dl + (size_t)x0 * 2, f_dl, (const uint8_t*)hb->disp_left + (size_t)f0 * hb->dl_frame + (size_t)x0 * 2, hb->dl_frame,
                                   hb->dl_step, (size_t)(x1 - x0) * 2, dh, nf, cudaMemcpyHostToDevice, st, (int64_t)dw * 2))) return cs;
-            read_window(useconf ? g.rrx : 0, g.rw, dw, 8, 32, &x0, &x1);
+            read_window(useconf ? g.rrx : 0, g.rw, dw, wmargin, 32, &x0, &x1);
             if (useconf && (cs = copy_frames(ctx, d_dr + (size_t)x0 * 2, f_dl, (const uint8_t*)hb->disp_right + (size_t)f0 * hb->dr_frame + (size_t)x0 * 2,
                                              hb->dr_frame, hb->dr_step, (size_t)(x1 - x0) * 2, dh, nf, cudaMemcpyHostToDevice, st, (int64_t)dw * 2))) return cs;
-            read_window(g.fx, g.fw, W, 8, 32, &x0, &x1);
+            read_window(g.fx, g.fw, W, wmargin, 32, &x0, &x1);
             if ((cs = copy_frames(ctx, d_view + (size_t)x0 * vcn, f_view, hb->view + (size_t)f0 * hb->view_frame + (size_t)x0 * vcn, hb->view_frame, hb->view_step,
                                   (size_t)(x1 - x0) * vcn, H, nf, cudaMemcpyHostToDevice, st, (int64_t)W * vcn))) return cs;
         }

@@ -128,14 +128,15 @@ def test_shard_frames_covers_batch():
 
 def test_weighted_shards_cover_batch():
     from addingdisparityfiltering_b200.batch import shard_frames, shard_frames_weighted
-    for n, world, extra in ((512, 8, 0), (512, 8, 8), (512, 8, 12), (512, 2, 5), (7, 4, 100), (512, 1, 9)):
+    for n, world, extra in ((512, 8, 0), (512, 8, 8), (512, 8, -24), (512, 8, -64), (512, 8, -100), (512, 2, 5), (7, 4, 100), (512, 1, 9), (5, 3, -1)):
         spans = [shard_frames_weighted(n, world, r, 0, extra) for r in range(world)]
         assert spans[0][0] == 0 and spans[-1][1] == n and all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
         sizes = [e - b for b, e in spans]
+        assert all(v >= 0 for v in sizes)
         if extra == 0 or world == 1:
             assert spans == [shard_frames(n, world, r) for r in range(world)]
         else:
-            assert sizes[0] >= max(sizes[1:]) and max(sizes[1:]) - min(sizes[1:]) <= 1 and sizes[0] - min(sizes[1:]) >= min(extra, n) - 1
+            assert sizes[0] == max(0, min(n, n // world + extra)) and max(sizes[1:]) - min(sizes[1:]) <= 1
 
 
 _WORKER = r'''

@@ -1,13 +1,5 @@
 #!/bin/bash
-# 8 GPUs: the sharded 512-frame batch with the NCCL gather inside the timed region, a few chunk plans; then N = 4
+# 8 GPUs, short: the gather root owns fewer frames than the other ranks (it also receives everybody's results)
 N=${1:-8}
-tools/scale_variants.sh $N "16 4 0" "32 0 0" "16 4 8" "8 2 0"
-grep -v "^\*\|OMP_NUM\|^$" gpurun_out/b${N}_0.err | tail -3
-# the driver's own command line for this N (default flags), kept as the profile record
-python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29777 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_r02_n$N.json 2> gpurun_out/bench_r02_n$N.err
-python - "gpurun_out/bench_r02_n$N.json" <<'PY'
-import json,sys
-for l in open(sys.argv[1]):
-    if l.startswith('{'):
-        d=json.loads(l); print("DEFAULT", d["n_gpus"], "value", round(d["value"]), "compute_only", round(d["compute_only"]["value"]), "e2e", round(d["e2e"]["value"]), round(d["e2e"]["with_confidence_map"]["value"]), "gather_in_timed_region", d["gather_in_timed_region"], d["run"]["chunk_plan_rank0"])
-PY
+tools/scale_variants.sh $N "16 4 -16" "16 4 -32" "16 4 -48" "32 8 -32" "16 4 -32 NCCL_MAX_P2P_NCHANNELS=4"
+grep -v "^\*\|OMP_NUM\|^$" gpurun_out/b${N}_4.err | tail -3
