@@ -52,6 +52,7 @@ EXPORTS = ["dwls_default_params", "dwls_ctx_create", "dwls_ctx_destroy", "dwls_l
            "dwls_kernel_launches", "dwls_set_group_frames", "dwls_set_lanes", "dwls_set_kernel_timing", "dwls_kernel_timing_report", "dwls_set_cuda_graphs", "dwls_set_plane_interleave", "dwls_graph_replays", "dwls_transfer_bytes", "dwls_filter_host", "dwls_filter_batch_dev",
            "dwls_filter_batch_host", "dwls_fgs_host", "dwls_fgs_dev", "dwls_lrc_mask_host", "dwls_fgs_weights_host",
            "dwls_fgs_dev_noalloc", "dwls_fgs_noalloc_scratch_bytes", "dwls_fgs_noalloc_required_bytes",
+           "dwls_peer_alloc", "dwls_peer_free", "dwls_peer_open", "dwls_peer_close", "dwls_peer_push", "dwls_peer_flush", "dwls_peer_bytes",
            "dwls_bm_default_params", "dwls_stereo_bm_dev", "dwls_stereo_bm_host", "dwls_halve_views_dev"]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -96,6 +97,14 @@ def lib():
             L.dwls_ctx_destroy.argtypes = [C.c_void_p]
             L.dwls_set_group_frames.argtypes = [C.c_void_p, C.c_int]
             L.dwls_set_lanes.argtypes = [C.c_void_p, C.c_int]
+            L.dwls_peer_alloc.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p), C.c_void_p]
+            L.dwls_peer_free.argtypes = [C.c_void_p, C.c_void_p]
+            L.dwls_peer_open.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
+            L.dwls_peer_close.argtypes = [C.c_void_p, C.c_void_p]
+            L.dwls_peer_push.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+            L.dwls_peer_flush.argtypes = [C.c_void_p, C.c_void_p]
+            L.dwls_peer_bytes.restype = C.c_int64
+            L.dwls_peer_bytes.argtypes = [C.c_void_p]
             L.dwls_set_kernel_timing.argtypes = [C.c_void_p, C.c_int]
             L.dwls_set_cuda_graphs.argtypes = [C.c_void_p, C.c_int]
             L.dwls_set_plane_interleave.argtypes = [C.c_void_p, C.c_int]

@@ -188,6 +188,13 @@ def chunk_plan(n_local, chunk, tail_min=0):
     return plan
 
 
+class _DeviceArray:
+    """A raw device allocation presented through __cuda_array_interface__ so that torch can view it without copying."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(int(v) for v in shape), "typestr": typestr, "data": (int(ptr), False), "version": 2, "strides": None}
+
+
 class ShardedBatch:
     """A batch of n_total independent frames sharded over the ranks of a process group (contiguous blocks,
     shard_frames), filtered chunk by chunk, with the CV_16S results gathered over NCCL WHILE the next chunk is computed.
@@ -198,9 +205,16 @@ class ShardedBatch:
     kernels of chunk k: torch's NCCL stream waits for them through an event and runs beside the kernels of chunk k+1 that
     are launched next on the compute stream; wait() joins the two streams at the end of the step.  The receives land
     directly at their final position in `full` (frame order of the unsharded batch) - no staging copy, no reorder pass;
-    a rank's own shard is a view of `full`, so the root's own results need no copy either."""
+    a rank's own shard is a view of `full`, so the root's own results need no copy either.
 
-    def __init__(self, n_total, frame_shape, chunk=16, tail_min=4, mode="root", dst=0, group=None, device=None, dtype=None, root_extra=0):
+    mode "peer": the same gather to rank `dst` without NCCL on the data path - the root's buffer is a CUDA IPC allocation every
+    rank maps, and a rank pushes each finished chunk to its final place with a peer-to-peer copy on a copy stream
+    (dwls_peer_push: copy engines over NVLink, no SM of either side), again overlapping the next chunk's kernels; wait() makes
+    the compute stream wait for the pushes and then synchronises the ranks with one 4-byte all-reduce, after which the root may
+    read.  Measured at 8 GPUs, NCCL send / recv from 7 peers into one root reaches about 0.4 TB/s, which bounds the step
+    (DESIGN.md section 6); int16 CUDA batches only."""
+
+    def __init__(self, n_total, frame_shape, chunk=16, tail_min=4, mode="root", dst=0, group=None, device=None, dtype=None, root_extra=0, ctx=None):
         import torch
         import torch.distributed as dist
         self.dist = dist if dist.is_available() and dist.is_initialized() else None
@@ -208,18 +222,91 @@ class ShardedBatch:
         self.world = self.dist.get_world_size(group) if self.dist else 1
         self.rank = self.dist.get_rank(group) if self.dist else 0
         self.n_total, self.mode, self.dst = n_total, mode, dst
-        self.spans = [shard_frames_weighted(n_total, self.world, r, dst, root_extra if mode == "root" else 0) for r in range(self.world)]
+        self.spans = [shard_frames_weighted(n_total, self.world, r, dst, root_extra if mode in ("root", "peer") else 0) for r in range(self.world)]
         self.begin, self.end = self.spans[self.rank]
         self.plans = [chunk_plan(e - b, chunk, tail_min) for b, e in self.spans]      # every rank can derive every peer's plan
         self.plan = self.plans[self.rank]
         holds_all = self.world == 1 or mode == "all" or self.rank == dst
         dtype = dtype or torch.int16
         n_alloc = n_total if holds_all else self.end - self.begin
-        self.full = torch.empty((n_alloc,) + tuple(frame_shape), dtype=dtype, device=device)
+        self._peer = None
+        if mode == "peer" and self.world > 1:
+            self._peer_setup(n_total, frame_shape, dtype, device, ctx, holds_all)
+        else:
+            self.full = torch.empty((n_alloc,) + tuple(frame_shape), dtype=dtype, device=device)
         self.local = self.full[self.begin:self.end] if holds_all else self.full
         self.holds_all = holds_all
         self._works = []
         self.bytes_sent = 0
+
+    def _peer_setup(self, n_total, frame_shape, dtype, device, ctx, is_root):
+        import torch
+        if dtype != torch.int16 or device is None or torch.device(device).type != "cuda":
+            raise _lib.DwlsError(_lib.DWLS_BAD_ARG, "gather mode 'peer' moves int16 CUDA batches")
+        device = torch.device(device)
+        self.ctx = ctx or _lib.default_context(device.index or 0)
+        L = _lib.lib()
+        self._frame_bytes = 2
+        for v in frame_shape:
+            self._frame_bytes *= int(v)
+        handle = torch.zeros(64, dtype=torch.uint8, device=device)
+        # A rank whose allocation / mapping fails must not leave the others hanging in a collective: everybody takes part in the
+        # handle broadcast and in one agreement all-reduce, and then ALL ranks raise together.
+        error = None
+        if is_root:
+            try:
+                ptr, hbuf = C.c_void_p(), (C.c_ubyte * 64)()
+                self.ctx.check(L.dwls_peer_alloc(self.ctx.handle, C.c_size_t(n_total * self._frame_bytes), C.byref(ptr), hbuf))
+                self.full = torch.as_tensor(_DeviceArray(ptr.value, (n_total,) + tuple(frame_shape), "<i2"), device=device)
+                assert self.full.data_ptr() == ptr.value and self.full.dtype == torch.int16
+                handle.copy_(torch.tensor(list(hbuf), dtype=torch.uint8))
+                self._peer = ("root", ptr.value)
+            except Exception as e:          # noqa: BLE001 - reported collectively below
+                error = e
+        self.dist.broadcast(handle, src=self.dst, group=self.group)
+        if not is_root:
+            try:
+                hb = (C.c_ubyte * 64)(*handle.cpu().tolist())
+                mapped = C.c_void_p()
+                self.ctx.check(L.dwls_peer_open(self.ctx.handle, hb, C.byref(mapped)))
+                self.full = torch.empty((self.end - self.begin,) + tuple(frame_shape), dtype=dtype, device=device)
+                self._peer = ("rank", mapped.value)
+            except Exception as e:          # noqa: BLE001
+                error = e
+        ok = torch.tensor([0 if error is not None else 1], dtype=torch.int32, device=device)
+        self.dist.all_reduce(ok, op=self.dist.ReduceOp.MIN, group=self.group)
+        if int(ok.item()) == 0:
+            kind_ptr, self._peer = self._peer, None
+            if kind_ptr is not None:        # undo what this rank did set up
+                if kind_ptr[0] == "rank":
+                    L.dwls_peer_close(self.ctx.handle, C.c_void_p(kind_ptr[1]))
+                else:
+                    self.full = None
+                    L.dwls_peer_free(self.ctx.handle, C.c_void_p(kind_ptr[1]))
+            raise _lib.DwlsError(_lib.DWLS_CUDA_ERROR, "peer-memory gather could not be set up on every rank (this rank: %s)" % (error if error is not None else "ok"))
+        self._token = torch.zeros(1, dtype=torch.int32, device=device)
+        self._device = device
+
+    def close(self):
+        """Releases the peer mapping / the root's IPC allocation (collective: every rank calls it once the buffer is no longer read)."""
+        if self._peer is None:
+            return
+        import torch
+        torch.cuda.synchronize(self._device)
+        self.dist.barrier(group=self.group)
+        kind, ptr = self._peer
+        self._peer = None
+        if kind == "rank":
+            self.ctx.check(_lib.lib().dwls_peer_close(self.ctx.handle, C.c_void_p(ptr)))
+            self.dist.barrier(group=self.group)
+        else:
+            self.dist.barrier(group=self.group)            # the other ranks have unmapped
+            self.full = self.local = None
+            self.ctx.check(_lib.lib().dwls_peer_free(self.ctx.handle, C.c_void_p(ptr)))
+
+    def _stream(self):
+        import torch
+        return torch.cuda.current_stream(self._device).cuda_stream or 1      # 1 = cudaStreamLegacy, torch's default stream
 
     def _wire(self, t):
         # the collective only moves bytes (NCCL has no int16 type, gloo no int16 kernels)
@@ -238,6 +325,14 @@ class ShardedBatch:
         dist = self.dist
         ops = []
         f0, nf = self.plan[k] if k < len(self.plan) else (0, 0)
+        if self._peer is not None:
+            if self._peer[0] == "rank" and nf:
+                src = self.local[f0:f0 + nf]
+                nbytes = nf * self._frame_bytes
+                self.ctx.check(_lib.lib().dwls_peer_push(self.ctx.handle, C.c_void_p(self._peer[1] + (self.begin + f0) * self._frame_bytes),
+                                                         C.c_void_p(src.data_ptr()), C.c_size_t(nbytes), C.c_void_p(self._stream())))
+                self.bytes_sent += nbytes
+            return
         mine = self._wire(self.local[f0:f0 + nf]) if nf else None
         if self.mode == "root":
             if self.rank == self.dst:
@@ -267,6 +362,10 @@ class ShardedBatch:
         for w in self._works:
             w.wait()
         self._works = []
+        if self._peer is not None:
+            if self._peer[0] == "rank":
+                self.ctx.check(_lib.lib().dwls_peer_flush(self.ctx.handle, C.c_void_p(self._stream())))
+            self.dist.all_reduce(self._token, group=self.group)      # stream-ordered after every rank's pushes: the root may read
 
     def run(self, filter_chunk, gather=True):
         """filter_chunk(first_local_frame, count, out_view) computes one chunk into out_view (asynchronously on the current

@@ -123,6 +123,8 @@ struct dwls_ctx {
     // device entry point records `busy` on its stream when it has queued its work, and the next one waits for it when it
     // runs on another stream (same stream: already ordered).
     cudaEvent_t busy = nullptr; cudaStream_t busy_stream = nullptr; bool busy_valid = false;
+    // peer-memory gather: copy stream of the pushes, producer / completion events, bytes pushed
+    cudaStream_t peer_stream = nullptr; cudaEvent_t peer_ev = nullptr, peer_done = nullptr; int64_t peer_bytes = 0;
     // device batch entry point: launch groups are dealt round-robin to `lanes` internal streams (forked from and joined
     // back into the caller's stream), each with its own workspace slice, so that the tail of one group's kernels overlaps
     // the head of another's; with small groups the planes a group hands from kernel to kernel stay in the 126 MB L2
@@ -260,6 +262,7 @@ void dwls_ctx_destroy(dwls_ctx* ctx)
     }
     if (ctx->xready) cudaEventDestroy(ctx->xready);
     if (ctx->busy) cudaEventDestroy(ctx->busy);
+    if (ctx->peer_stream) { cudaStreamSynchronize(ctx->peer_stream); cudaStreamDestroy(ctx->peer_stream); cudaEventDestroy(ctx->peer_ev); cudaEventDestroy(ctx->peer_done); }
     for (int l = 0; l < DWLS_MAX_LANES; ++l) { if (ctx->lane_st[l]) cudaStreamDestroy(ctx->lane_st[l]); if (ctx->lane_ev[l]) cudaEventDestroy(ctx->lane_ev[l]); }
     if (ctx->fork_ev) cudaEventDestroy(ctx->fork_ev);
     for (auto& sp : ctx->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -1736,3 +1739,89 @@ extern "C" dwls_status dwls_fgs_dev_noalloc(dwls_ctx* ctx, const dwls_image* gui
     ctx->launches++;
     return DWLS_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// peer-memory gather (one process per GPU on one NVLink / NVSwitch box; no counterpart in the reference, whose path is
+// single-process).  The gather root allocates the buffer of the whole batch with dwls_peer_alloc and hands its 64-byte CUDA
+// IPC handle to the other ranks (any byte transport: the Python side broadcasts it with torch.distributed); they map it with
+// dwls_peer_open and PUSH every finished chunk of CV_16S results straight to its final place with a peer-to-peer
+// cudaMemcpyAsync on a copy stream - the copy engines move the bytes over NVLink, no SM of the sender or of the root is
+// involved - ordered after the kernels that produced the chunk and overlapping the kernels of the next one.
+// (Why not NCCL send / recv: measured at 8 GPUs, 7 peers sending to one root reach about 0.4 TB/s into it - a few channels,
+// i.e. CTAs, per peer - which bounds the whole step)
+// ---------------------------------------------------------------------------------------------
+extern "C" dwls_status dwls_peer_alloc(dwls_ctx* ctx, size_t bytes, void** dev_ptr, unsigned char* handle64)
+{
+    if (!ctx || !dev_ptr || !handle64 || bytes == 0) return ctx ? fail(ctx, DWLS_BAD_ARG, "dwls_peer_alloc: bad argument") : DWLS_BAD_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    CK(cudaSetDevice(ctx->device));
+    void* p = nullptr;
+    CK(cudaMalloc(&p, bytes));
+    cudaIpcMemHandle_t h;
+    const cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); ctx->err = std::string("cudaIpcGetMemHandle failed: ") + cudaGetErrorString(e); return DWLS_CUDA_ERROR; }
+    memcpy(handle64, &h, 64);
+    *dev_ptr = p;
+    return DWLS_OK;
+}
+
+extern "C" dwls_status dwls_peer_free(dwls_ctx* ctx, void* dev_ptr)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaFree(dev_ptr));
+    return DWLS_OK;
+}
+
+extern "C" dwls_status dwls_peer_open(dwls_ctx* ctx, const unsigned char* handle64, void** mapped)
+{
+    if (!ctx || !handle64 || !mapped) return ctx ? fail(ctx, DWLS_BAD_ARG, "dwls_peer_open: bad argument") : DWLS_BAD_ARG;
+    CK(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    CK(cudaIpcOpenMemHandle(mapped, h, cudaIpcMemLazyEnablePeerAccess));
+    return DWLS_OK;
+}
+
+extern "C" dwls_status dwls_peer_close(dwls_ctx* ctx, void* mapped)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaIpcCloseMemHandle(mapped));
+    return DWLS_OK;
+}
+
+// copy `bytes` from local device memory to mapped peer memory on the context's copy stream, after everything queued so far on
+// `after_stream` (the stream the producing kernels were launched on); returns at once
+extern "C" dwls_status dwls_peer_push(dwls_ctx* ctx, void* dst_mapped, const void* src, size_t bytes, void* after_stream)
+{
+    if (!ctx || !dst_mapped || !src) return ctx ? fail(ctx, DWLS_BAD_ARG, "dwls_peer_push: bad argument") : DWLS_BAD_ARG;
+    if (bytes == 0) return DWLS_OK;
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->peer_stream) {
+        CK(cudaStreamCreateWithFlags(&ctx->peer_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->peer_ev, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&ctx->peer_done, cudaEventDisableTiming));
+    }
+    cudaStream_t prod = after_stream ? (cudaStream_t)after_stream : ctx->stream;
+    CK(cudaEventRecord(ctx->peer_ev, prod));
+    CK(cudaStreamWaitEvent(ctx->peer_stream, ctx->peer_ev, 0));
+    CK(cudaMemcpyAsync(dst_mapped, src, bytes, cudaMemcpyDefault, ctx->peer_stream));
+    ctx->peer_bytes += (int64_t)bytes;
+    return DWLS_OK;
+}
+
+// `stream` waits for every push issued so far
+extern "C" dwls_status dwls_peer_flush(dwls_ctx* ctx, void* stream)
+{
+    if (!ctx) return DWLS_BAD_ARG;
+    if (!ctx->peer_stream) return DWLS_OK;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaEventRecord(ctx->peer_done, ctx->peer_stream));
+    CK(cudaStreamWaitEvent(stream ? (cudaStream_t)stream : ctx->stream, ctx->peer_done, 0));
+    return DWLS_OK;
+}
+
+extern "C" int64_t dwls_peer_bytes(const dwls_ctx* ctx) { return ctx ? ctx->peer_bytes : 0; }

@@ -363,7 +363,8 @@ def main():
     ap.add_argument("--frames", type=int, default=512, help="frames of the whole batch per step (sharded over the GPUs)")
     ap.add_argument("--chunk", type=int, default=0, help="frames per launch / gather chunk (0 = 32 on one or two GPUs, 16 on more)")
     ap.add_argument("--tail-min", type=int, default=-1, help="smallest halved tail chunk (-1 = none on one or two GPUs, 4 on more)")
-    ap.add_argument("--gather-mode", default="root", choices=["root", "all"])
+    ap.add_argument("--gather-mode", default="auto", choices=["auto", "root", "all", "peer"],
+                    help="auto = peer-memory pushes (CUDA IPC + copy engines), NCCL send/recv to the root if that cannot be set up")
     ap.add_argument("--root-extra", type=int, default=0, help="frames the gather root owns beyond an even share (its results need no transfer)")
     ap.add_argument("--group", type=int, default=0, help="frames per kernel launch group inside a chunk (0 = library default)")
     ap.add_argument("--lanes", type=int, default=0, help="internal streams the launch groups of a chunk are dealt to (0 = library default)")
@@ -411,7 +412,15 @@ def main():
         for fr in tb:
             for t in fr:
                 dist.broadcast(t.view(torch.uint8), src=0)
-    sb = ShardedBatch(args.frames, (H, W), chunk=chunk, tail_min=tail_min, mode=args.gather_mode, dst=0, device=dev, root_extra=args.root_extra)
+    gather_mode = "peer" if args.gather_mode == "auto" else args.gather_mode
+    fallback = None
+    try:
+        sb = ShardedBatch(args.frames, (H, W), chunk=chunk, tail_min=tail_min, mode=gather_mode, dst=0, device=dev, root_extra=args.root_extra, ctx=ctx)
+    except A.DwlsError as e:                 # raised on every rank together (ShardedBatch._peer_setup)
+        if args.gather_mode != "auto":
+            raise
+        fallback, gather_mode = str(e), "root"
+        sb = ShardedBatch(args.frames, (H, W), chunk=chunk, tail_min=tail_min, mode=gather_mode, dst=0, device=dev, root_extra=args.root_extra, ctx=ctx)
     nloc = sb.end - sb.begin
 
     def build(k):          # frame f of the batch = base frame f % N_BASE rolled by 3 f columns (left / right / view alike)
@@ -561,8 +570,13 @@ def main():
     cfg = base_config(args.frames, world, source, chunk)
     run = {"frames_per_gpu": [e - b for b, e in sb.spans], "chunk_plan_rank0": [c for _, c in sb.plan],
            "gather": "none (one rank holds the whole batch)" if world == 1 else
-                     "CV_16S results of every chunk sent to rank 0 with grouped ncclSend/ncclRecv on NCCL's stream while the next "
-                     "chunk's kernels run (mode %s)" % args.gather_mode,
+                     {"peer": "CV_16S results of every chunk pushed into rank 0's buffer (CUDA IPC mapping) with peer-to-peer copies on a copy "
+                              "stream - copy engines over NVLink, no SMs - while the next chunk's kernels run; one 4-byte NCCL all-reduce per "
+                              "step orders the root's reads after the pushes",
+                      "root": "CV_16S results of every chunk sent to rank 0 with grouped ncclSend/ncclRecv on NCCL's stream while the next "
+                              "chunk's kernels run",
+                      "all": "every rank receives every chunk (grouped ncclSend/ncclRecv between all pairs)"}[gather_mode],
+           "gather_mode": gather_mode, "gather_fallback": fallback,
            "gather_in_timed_region": world > 1, "zero_confidence_share_of_roi": round(zero_conf, 4)}
     line = {
         "metric": METRIC, "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

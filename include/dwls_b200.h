@@ -166,6 +166,21 @@ DWLS_API dwls_status dwls_fgs_dev_noalloc(dwls_ctx* ctx, const dwls_image* guide
 DWLS_API size_t      dwls_fgs_noalloc_scratch_bytes(void);
 DWLS_API size_t      dwls_fgs_noalloc_required_bytes(int cols, int rows, int channels);
 
+/* ---- peer-memory gather of a sharded batch (one process per GPU, one NVLink / NVSwitch box) --------------------------
+ * No counterpart in the reference (its path is single-process); this is the exchange step of SURVEY section 8e.  The gather
+ * root allocates the buffer of the whole batch (dwls_peer_alloc: cudaMalloc + 64-byte CUDA IPC handle, which the caller
+ * transports to the other ranks), they map it (dwls_peer_open) and push every finished chunk of results to its final place
+ * with a peer-to-peer copy on the context's copy stream (dwls_peer_push: ordered after the work queued on `after_stream`,
+ * returns at once; copy engines over NVLink, no SM involved).  dwls_peer_flush makes a stream wait for all pushes issued so
+ * far; the caller then synchronises the ranks (any stream-ordered collective) before the root reads the buffer. */
+DWLS_API dwls_status dwls_peer_alloc(dwls_ctx* ctx, size_t bytes, void** dev_ptr, unsigned char* handle64);
+DWLS_API dwls_status dwls_peer_free(dwls_ctx* ctx, void* dev_ptr);
+DWLS_API dwls_status dwls_peer_open(dwls_ctx* ctx, const unsigned char* handle64, void** mapped);
+DWLS_API dwls_status dwls_peer_close(dwls_ctx* ctx, void* mapped);
+DWLS_API dwls_status dwls_peer_push(dwls_ctx* ctx, void* dst_mapped, const void* src, size_t bytes, void* after_stream);
+DWLS_API dwls_status dwls_peer_flush(dwls_ctx* ctx, void* stream);
+DWLS_API int64_t     dwls_peer_bytes(const dwls_ctx* ctx);
+
 /* ---- parity / debug exports ------------------------------------------------------------------
  * LRC decision per disparity pixel: 0 outside the ROI, 1 right index outside the right ROI
  * (confidence kept), 2 consistent (min of both confidences), 3 inconsistent (confidence 0). */

@@ -36,7 +36,11 @@ def main():
         dev = torch.device("cpu")
         dist.init_process_group("gloo", **init)
     H, W = (48, 64) if backend == "gloo" else (240, 320)
-    sb = ShardedBatch(n_total, (H, W), chunk=3, tail_min=1, mode=mode, dst=0, device=dev)
+    ctx = None
+    if backend == "nccl":
+        import addingdisparityfiltering_b200 as A
+        ctx = A.Context(dev.index)
+    sb = ShardedBatch(n_total, (H, W), chunk=3, tail_min=1, mode=mode, dst=0, device=dev, ctx=ctx)
     assert sb.spans[rank] == (sb.begin, sb.end) and sum(e - b for b, e in sb.spans) == n_total
 
     if backend == "gloo":
@@ -52,10 +56,8 @@ def main():
             else:
                 assert full.shape[0] == sb.end - sb.begin
     else:
-        import addingdisparityfiltering_b200 as A
         from addingdisparityfiltering_b200 import synth
         from addingdisparityfiltering_b200.batch import BatchFilter
-        ctx = A.Context(dev.index)
         frames = [synth.make_textured_scene(W, H, 3, seed=50 + f, max_disp=40) for f in range(n_total)]   # the same batch on every rank
         roi = (40, 0, W - 40, H)
         tv, tl, tr = [torch.from_numpy(np.stack([fr[k] for fr in frames])).to(dev) for k in range(3)]
@@ -74,6 +76,9 @@ def main():
             torch.cuda.synchronize()
             assert torch.equal(full, alone), "gathered batch differs from the single-GPU batch"
             assert ctx.kernel_launches() > 0
+        if mode == "peer":
+            assert (sb.bytes_sent > 0) == (rank != 0)
+        sb.close()
     dist.barrier()
     dist.destroy_process_group()
     print("ok rank %d/%d %s %s" % (rank, world, backend, mode))

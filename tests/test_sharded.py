@@ -42,7 +42,7 @@ def test_chunk_plan_covers_shard():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode", ["root", "all"])
+@pytest.mark.parametrize("mode", ["root", "all", "peer"])
 def test_sharded_filter_two_gpus_nccl(mode):
     import torch
     if torch.cuda.device_count() < 2:
