@@ -1554,11 +1554,21 @@ static dwls_status bm_frames(dwls_ctx* ctx, const uint8_t* left, int64_t l_step,
     const int width1 = std::max(run0 ? P0.width1 : 0, run1 ? P1.width1 : 0);
     const size_t smem = std::max(P0.smem, P1.smem);
     if (smem > 200 * 1024) return fail(ctx, DWLS_UNSUPPORTED, "numDisparities x window too large for the device matcher's shared memory");
-    if (ctx->smem_attr_done.insert((const void*)bm_kernel).second || smem > 48 * 1024)
-        CK(cudaFuncSetAttribute(bm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    // the window size is a template parameter of the kernel (unrolled taps); sizes without an instantiation take the looped one
+    const int need_g = std::max(run0 ? (P0.wc * (a0.ndisp / 4) + BM_T - 1) / BM_T : 0, run1 ? (P1.wc * (a1.ndisp / 4) + BM_T - 1) / BM_T : 0);
+    const bool small = need_g <= 8;
+    void (*kern)(const BmArgs, const BmArgs) = small ? bm_kernel<0, 8> : bm_kernel<0, BM_MAXG>;
+#define DWLS_BM_CASE(W) case W: kern = small ? bm_kernel<W, 8> : bm_kernel<W, BM_MAXG>; break;
+    switch (p->block_size) {
+    DWLS_BM_CASE(5) DWLS_BM_CASE(7) DWLS_BM_CASE(9) DWLS_BM_CASE(11) DWLS_BM_CASE(13) DWLS_BM_CASE(15) DWLS_BM_CASE(17) DWLS_BM_CASE(19) DWLS_BM_CASE(21)
+    default: break;
+    }
+#undef DWLS_BM_CASE
+    if (ctx->smem_attr_done.insert((const void*)kern).second || smem > 48 * 1024)
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
     if (!run0) { a0 = a1; }                                                  // (cannot happen for a left matcher with a valid right one; kept total)
     (void)views;
-    TIMED(K_BM, st, bm_kernel<<<dim3((width1 + BM_TW - 1) / BM_TW, (P0.y1 - P0.y0 + BM_RB - 1) / BM_RB, 2 * frames), BM_T, smem, st>>>(a0, run1 ? a1 : a0));
+    TIMED(K_BM, st, kern<<<dim3((width1 + BM_TW - 1) / BM_TW, (P0.y1 - P0.y0 + BM_RB - 1) / BM_RB, 2 * frames), BM_T, smem, st>>>(a0, run1 ? a1 : a0));
     CK(cudaGetLastError());
     return DWLS_OK;
 }

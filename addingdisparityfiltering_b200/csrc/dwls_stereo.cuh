@@ -68,16 +68,21 @@ __global__ void __launch_bounds__(256) bm_prefilter_kernel(const PrefArgs a)
 // column cr[c] + d, i.e. disparity ndisp - 1 - d + mindisp).  For every row the CTA
 //   A. updates the vertical window sums V[c][d] = sum over the wsz rows of |L - R| (row entering minus row leaving; the
 //      sums live in registers, two 16-bit sums per register, four d per thread and step),
-//   B. publishes them to shared memory,
-//   C. forms SAD[x][d] = sum_{c = x .. x + wsz - 1} V[c][d] (thread = (x, quarter of the d range)), keeps the first minimum,
+//   B. publishes them to shared memory as V2[d / 2][c] (column fastest),
+//   C. forms SAD[x][d] = sum_{c = x .. x + wsz - 1} V[c][d] (thread = (x, quarter of the d range)): wsz CONSECUTIVE words
+//      per pair of candidates, keeps the first minimum,
 //   D. merges the four quarters, applies the texture / uniqueness tests and the parabola fit, and stores the CV_16S value.
 // Pixels outside StereoBM's valid-disparity rectangle get FILTERED = (mindisp - 1) * 16.
+// The kernel is bound by instruction issue (ncu, round 2: issue slots 68 % active, DRAM 0.06 %), so everything that does
+// not depend on the row is computed once: the window size is a template parameter (WSZ = 0: any size, looped), and the
+// (column, candidates) groups a thread owns are described by ONE packed register each, set up before the row loop
+// (column | offset of the right view's bytes in a staged row | index of the pair of sums in V2).
 // grid = (ceil(width1 / BM_TW), ceil(valid rows / BM_RB), frames * 2 views), block = 256
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int BM_TW = 64, BM_RB = 32, BM_T = 256;
 constexpr int BM_MAXG = 16;      // (c, 4 d) groups a thread may own: (BM_TW + wsz - 1) * ndisp / 4 / BM_T <= BM_MAXG
 
-struct BmPlan { int lofs, rofs, width1, y0, y1, xmin, xmax, wc, np, vpitch, rw; size_t smem; bool ok; };
+struct BmPlan { int lofs, rofs, width1, y0, y1, xmin, xmax, wc, np, rw, lpitch; size_t smem; bool ok; };
 
 __host__ __device__ inline BmPlan bm_plan(int w, int h, int ndisp, int wsz, int mindisp)
 {
@@ -91,24 +96,26 @@ __host__ __device__ inline BmPlan bm_plan(int w, int h, int ndisp, int wsz, int 
     p.xmax = (w < w - mindisp ? w : w - mindisp) - w2;
     p.wc = BM_TW + wsz - 1;                     // window columns per tile
     p.np = ndisp / 2;                           // packed pairs of d
-    p.vpitch = p.np | 1;                        // odd number of words per window column: conflict-free column walks
+    p.lpitch = (p.wc + 3) & ~3;                 // staged left row (bytes)
     p.rw = (p.wc + ndisp + 3 + 3) & ~3;         // staged right row: wc + ndisp - 1 bytes (+ slack for word reads), multiple of 4
     const int rows = BM_RB + wsz - 1;
-    p.smem = (size_t)rows * ((p.wc + 3) & ~3) + (size_t)rows * p.rw + (size_t)p.wc * p.vpitch * 4 + (size_t)p.wc * 4 * 3 + (size_t)BM_T * 8 + 64;
+    p.smem = (size_t)rows * p.lpitch + (size_t)rows * p.rw + (size_t)p.np * p.wc * 4 + (size_t)p.wc * 4 + (size_t)BM_T * 8 + 64;
+    // packed group descriptor: column < 256, right offset < 512, V2 index < 32768
     p.ok = p.lofs < w && p.rofs < w && p.width1 >= 1 && p.y1 > p.y0 && ndisp % 16 == 0 && ndisp >= 16 && (wsz & 1) && wsz >= 5 &&
-           (p.wc * (ndisp / 4) + BM_T - 1) / BM_T <= BM_MAXG;
+           (p.wc * (ndisp / 4) + BM_T - 1) / BM_T <= BM_MAXG && p.wc < 256 && p.rw <= 512 && p.np * p.wc < 32768;
     return p;
 }
 
-__device__ __forceinline__ uint32_t bm_absdiff4(uint32_t l4, uint32_t r4) { return __vabsdiffu4(l4, r4); }
-
+// MAXG: groups a thread can own (8 or BM_MAXG = 16): the descriptors and running sums are registers, so the smaller capacity
+// is used whenever the window columns x candidates of a tile fit it (e.g. 80 candidates, window 7: 6 groups per thread)
+template <int WSZ, int MAXG>
 __global__ void __launch_bounds__(BM_T) bm_kernel(const BmArgs a0, const BmArgs a1)
 {
     extern __shared__ __align__(16) uint8_t bsm[];
     const int view = blockIdx.z & 1, frame = blockIdx.z >> 1;
     if (view == 1 && a1.disp == a0.disp) return;              // one matcher only: the second view's blocks have nothing to do
     const BmArgs& a = view ? a1 : a0;
-    const int w = a.w, h = a.h, ndisp = a.ndisp, wsz = a.wsz, w2 = wsz / 2;
+    const int w = a.w, h = a.h, ndisp = a.ndisp, wsz = WSZ ? WSZ : a.wsz, w2 = wsz / 2;
     const BmPlan P = bm_plan(w, h, ndisp, wsz, a.mindisp);
     const int FILTERED = (a.mindisp - 1) * 16;
     const int tid = threadIdx.x;
@@ -117,14 +124,12 @@ __global__ void __launch_bounds__(BM_T) bm_kernel(const BmArgs a0, const BmArgs 
     if (x0 >= P.width1 || yb >= P.y1) return;                 // (uniform) tiles of the other view's larger grid
     const int rows_out = min(BM_RB, P.y1 - yb);
     const int rows = rows_out + wsz - 1;                      // staged rows yb - w2 .. yb + rows_out - 1 + w2
-    const int lpitch = (P.wc + 3) & ~3;
+    const int lpitch = P.lpitch, rw = P.rw, wc = P.wc;
     uint8_t* Ls = bsm;                                         // [rows][lpitch]
     uint8_t* Rs = Ls + (size_t)(BM_RB + wsz - 1) * lpitch;     // [rows][rw]
-    uint32_t* V2 = (uint32_t*)(Rs + (size_t)(BM_RB + wsz - 1) * P.rw);   // [wc][vpitch] packed pairs of 16-bit sums
-    int* roff = (int*)(V2 + (size_t)P.wc * P.vpitch);          // [wc] offset of cr[c] inside a staged right row
-    int* T = roff + P.wc;                                      // [wc] vertical texture sums
-    int* spare = T + P.wc;                                     // [wc]
-    int2* red = (int2*)(((uintptr_t)(spare + P.wc) + 7) & ~(uintptr_t)7);   // [BM_T] (minsad, mind) per thread
+    uint32_t* V2 = (uint32_t*)(Rs + (size_t)(BM_RB + wsz - 1) * rw);   // [np][wc] packed pairs of 16-bit sums, column fastest
+    int* T = (int*)(V2 + (size_t)P.np * wc);                   // [wc] vertical texture sums
+    int2* red = (int2*)(((uintptr_t)(T + wc) + 7) & ~(uintptr_t)7);   // [BM_T] (minsad, mind) per thread
     const uint8_t* Lg = a.left + (size_t)frame * a.l_frame;
     const uint8_t* Rg = a.right + (size_t)frame * a.r_frame;
     int16_t* Dg = a.disp + (size_t)frame * a.d_frame;
@@ -134,85 +139,109 @@ __global__ void __launch_bounds__(BM_T) bm_kernel(const BmArgs a0, const BmArgs 
     auto colL = [&](int c) { return min(max(xr0 + c, -P.lofs), w - P.lofs - 1) + P.lofs; };
     auto colR = [&](int c) { return min(max(xr0 + c, -P.rofs), w - P.rofs - ndisp) + P.rofs; };
     const int rbase = colR(0);                                 // cr[] is non-decreasing: staged right columns rbase ..
-    const int rcols = colR(P.wc - 1) + ndisp - rbase;          // .. rbase + rcols - 1  (<= wc + ndisp - 1)
-    for (int c = tid; c < P.wc; c += BM_T) roff[c] = colR(c) - rbase;
-    for (int idx = tid; idx < rows * P.wc; idx += BM_T) {
-        const int r = idx / P.wc, c = idx - r * P.wc;
+    const int rcols = colR(wc - 1) + ndisp - rbase;            // .. rbase + rcols - 1  (<= wc + ndisp - 1)
+    for (int idx = tid; idx < rows * wc; idx += BM_T) {
+        const int r = idx / wc, c = idx - r * wc;
         Ls[r * lpitch + c] = Lg[(size_t)(yb - w2 + r) * a.l_step + colL(c)];
     }
-    for (int idx = tid; idx < rows * P.rw; idx += BM_T) {
-        const int r = idx / P.rw, j = idx - r * P.rw;
-        Rs[r * P.rw + j] = j < rcols ? Rg[(size_t)(yb - w2 + r) * a.r_step + rbase + j] : (uint8_t)0;
+    for (int idx = tid; idx < rows * rw; idx += BM_T) {
+        const int r = idx / rw, j = idx - r * rw;
+        Rs[r * rw + j] = j < rcols ? Rg[(size_t)(yb - w2 + r) * a.r_step + rbase + j] : (uint8_t)0;
+    }
+
+    // ---- the (window column, 4 candidates) groups of this thread, column fastest: g = d4 * wc + c ----
+    const int nd4 = ndisp >> 2, ngroups = wc * nd4;
+    uint32_t desc[MAXG];                                    // c | offR << 8 | vidx << 17
+    int nk = 0;
+#pragma unroll
+    for (int k = 0; k < MAXG; ++k) {
+        const int g = tid + k * BM_T;
+        desc[k] = 0;
+        if (g < ngroups) {
+            const int d4 = g / wc, c = g - d4 * wc;
+            const int offR = colR(c) - rbase + 4 * d4;         // bytes from the start of a staged right row
+            desc[k] = (uint32_t)c | ((uint32_t)offR << 8) | ((uint32_t)(2 * d4 * wc + c) << 17);
+            nk = k + 1;
+        }
     }
     __syncthreads();
 
-    // ---- groups of (window column, 4 candidates) owned by this thread ----
-    const int nd4 = ndisp >> 2, ngroups = P.wc * nd4;
-    uint32_t v01[BM_MAXG], v23[BM_MAXG];                       // 16-bit vertical sums of candidates d, d+1 | d+2, d+3
+    uint32_t v01[MAXG], v23[MAXG];                       // 16-bit vertical sums of candidates d, d+1 | d+2, d+3
 #pragma unroll
-    for (int k = 0; k < BM_MAXG; ++k) { v01[k] = 0; v23[k] = 0; }
-    auto diff4 = [&](int r, int c, int d) {                   // |L - R| for candidates d .. d+3 of window column c, staged row r
-        const uint32_t l4 = (uint32_t)Ls[r * lpitch + c] * 0x01010101u;
-        const uint8_t* rp = Rs + r * P.rw + roff[c] + d;
-        const uint32_t* wp = (const uint32_t*)((uintptr_t)rp & ~(uintptr_t)3);
-        const uint32_t r4 = __funnelshift_r(wp[0], wp[1], (int)(((uintptr_t)rp & 3) * 8));
-        return bm_absdiff4(l4, r4);
+    for (int k = 0; k < MAXG; ++k) { v01[k] = 0; v23[k] = 0; }
+    // |L - R| for the 4 candidates of a group in staged row r (Lrow / Rrow = that row's bytes; rows are word aligned)
+    auto diff4 = [&](const uint8_t* Lrow, const uint8_t* Rrow, uint32_t dsc) {
+        const uint32_t l4 = (uint32_t)Lrow[dsc & 0xffu] * 0x01010101u;
+        const uint32_t off = (dsc >> 8) & 0x1ffu;
+        const uint32_t* wp = (const uint32_t*)(Rrow + (off & ~3u));
+        const uint32_t r4 = __funnelshift_r(wp[0], wp[1], (int)((off & 3u) * 8u));
+        return __vabsdiffu4(l4, r4);
     };
     const bool want_tex = a.texture > 0;
     int tsum_c = 0;                                            // this thread's texture column (tid < wc)
     // warm-up: the first wsz - 1 rows of the window of output row yb
     for (int r = 0; r < wsz - 1; ++r) {
+        const uint8_t* Lrow = Ls + r * lpitch; const uint8_t* Rrow = Rs + r * rw;
 #pragma unroll
-        for (int k = 0; k < BM_MAXG; ++k) {
-            const int gi = tid + k * BM_T;
-            if (gi < ngroups) {
-                const int c = gi / nd4, d = (gi - c * nd4) * 4;
-                const uint32_t df = diff4(r, c, d);
+        for (int k = 0; k < MAXG; ++k)
+            if (k < nk) {
+                const uint32_t df = diff4(Lrow, Rrow, desc[k]);
                 v01[k] += __byte_perm(df, 0, 0x4140); v23[k] += __byte_perm(df, 0, 0x4342);
             }
-        }
-        if (want_tex && tid < P.wc) tsum_c += abs((int)Ls[r * lpitch + tid] - a.ftzero);
+        if (want_tex && tid < wc) tsum_c += abs((int)Lrow[tid] - a.ftzero);
     }
 
     const int xq = tid & (BM_TW - 1), q = tid / BM_TW;         // phase C: output column of the tile, quarter of the d range
     const int dq0 = q * (ndisp / 4), dq1 = dq0 + ndisp / 4;    // candidates of this quarter (multiples of 4)
     auto sad_at = [&](int x, int d) {                          // SAD of candidate d at tile column x from the published sums
+        const uint32_t* p = V2 + (d >> 1) * wc + x;
         int s = 0;
-        for (int c = x; c < x + wsz; ++c) { const uint32_t v = V2[c * P.vpitch + (d >> 1)]; s += (d & 1) ? (int)(v >> 16) : (int)(v & 0xffffu); }
+        for (int k = 0; k < wsz; ++k) { const uint32_t v = p[k]; s += (d & 1) ? (int)(v >> 16) : (int)(v & 0xffffu); }
         return s;
     };
 
     for (int yo = 0; yo < rows_out; ++yo) {
         // A. row yo + wsz - 1 enters; row yo - 1 leaves (after the first output row)
+        {
+            const uint8_t* Lin = Ls + (yo + wsz - 1) * lpitch; const uint8_t* Rin = Rs + (yo + wsz - 1) * rw;
+            const uint8_t* Lout = Ls + max(yo - 1, 0) * lpitch; const uint8_t* Rout = Rs + max(yo - 1, 0) * rw;
 #pragma unroll
-        for (int k = 0; k < BM_MAXG; ++k) {
-            const int gi = tid + k * BM_T;
-            if (gi < ngroups) {
-                const int c = gi / nd4, d = (gi - c * nd4) * 4;
-                const uint32_t dn = diff4(yo + wsz - 1, c, d);
-                v01[k] += __byte_perm(dn, 0, 0x4140); v23[k] += __byte_perm(dn, 0, 0x4342);
-                if (yo > 0) {
-                    const uint32_t dl = diff4(yo - 1, c, d);
-                    v01[k] -= __byte_perm(dl, 0, 0x4140); v23[k] -= __byte_perm(dl, 0, 0x4342);
+            for (int k = 0; k < MAXG; ++k)
+                if (k < nk) {
+                    const uint32_t dsc = desc[k];
+                    const uint32_t dn = diff4(Lin, Rin, dsc);
+                    v01[k] += __byte_perm(dn, 0, 0x4140); v23[k] += __byte_perm(dn, 0, 0x4342);
+                    if (yo > 0) {
+                        const uint32_t dl = diff4(Lout, Rout, dsc);
+                        v01[k] -= __byte_perm(dl, 0, 0x4140); v23[k] -= __byte_perm(dl, 0, 0x4342);
+                    }
+                    // B. publish (sums stay below 2^16: wsz^2 * 2 * cap < 65536, checked on the host)
+                    uint32_t* vp = V2 + (dsc >> 17);
+                    vp[0] = v01[k]; vp[wc] = v23[k];
                 }
-                // B. publish (sums stay below 2^16: wsz^2 * 2 * cap <= 21 * 21 * 126 < 65536, checked on the host)
-                V2[c * P.vpitch + (d >> 1)] = v01[k]; V2[c * P.vpitch + (d >> 1) + 1] = v23[k];
+            if (want_tex && tid < wc) {
+                tsum_c += abs((int)Lin[tid] - a.ftzero);
+                if (yo > 0) tsum_c -= abs((int)Lout[tid] - a.ftzero);
+                T[tid] = tsum_c;
             }
-        }
-        if (want_tex && tid < P.wc) {
-            tsum_c += abs((int)Ls[(yo + wsz - 1) * lpitch + tid] - a.ftzero);
-            if (yo > 0) tsum_c -= abs((int)Ls[(yo - 1) * lpitch + tid] - a.ftzero);
-            T[tid] = tsum_c;
         }
         __syncthreads();
         // C. first minimum over this quarter's candidates
         int minsad = 0x7fffffff, mind = -1;
-        for (int d = dq0; d < dq1; d += 2) {
-            uint32_t s2 = 0;
-            for (int c = xq; c < xq + wsz; ++c) s2 += V2[c * P.vpitch + (d >> 1)];     // both 16-bit halves at once (no carry: see B)
-            const int s0 = (int)(s2 & 0xffffu), s1 = (int)(s2 >> 16);
-            if (s0 < minsad) { minsad = s0; mind = d; }
-            if (s1 < minsad) { minsad = s1; mind = d + 1; }
+        {
+            const uint32_t* p = V2 + (dq0 >> 1) * wc + xq;
+            for (int d = dq0; d < dq1; d += 2, p += wc) {
+                uint32_t s2 = 0;                                // both 16-bit halves at once (no carry: see B)
+                if (WSZ) {
+#pragma unroll
+                    for (int k = 0; k < (WSZ ? WSZ : 1); ++k) s2 += p[k];
+                } else {
+                    for (int k = 0; k < wsz; ++k) s2 += p[k];
+                }
+                const int s0 = (int)(s2 & 0xffffu), s1 = (int)(s2 >> 16);
+                if (s0 < minsad) { minsad = s0; mind = d; }
+                if (s1 < minsad) { minsad = s1; mind = d + 1; }
+            }
         }
         red[tid] = make_int2(minsad, mind);
         __syncthreads();
