@@ -1005,7 +1005,10 @@ static size_t elem_size(int depth) { return depth == DWLS_8U ? 1 : depth == DWLS
 // copy stream, a slab moving in chunks so that the host-side memcpy of one chunk overlaps the DMA of another.
 // ---------------------------------------------------------------------------------------------
 struct XferJob { uint8_t* host; int64_t hstep; size_t row_bytes; int rows; uint8_t* dev; size_t pin_off; };
-static const int XFER_T = 4;
+#ifndef DWLS_XFER_T
+#define DWLS_XFER_T 4
+#endif
+static const int XFER_T = DWLS_XFER_T;          // host threads (and copy streams) of a staged transfer, at most 8
 static const size_t XFER_MIN = (size_t)2 << 20, XFER_CHUNK = (size_t)1 << 20;
 
 static dwls_status xfer_prepare(dwls_ctx* ctx, XferJob* jobs, int n, size_t* total)

@@ -66,8 +66,11 @@ __device__ __forceinline__ int wt_dist2(uint32_t a, uint32_t b)
     return (int)__dp4a(d, d, 0u);
 }
 
+#ifndef DWLS_WT_MINB
+#define DWLS_WT_MINB 4
+#endif
 template <int CN>
-__global__ void __launch_bounds__(256) weights_kernel(const uint8_t* __restrict__ guide, int64_t gstep, int64_t gframe,
+__global__ void __launch_bounds__(256, DWLS_WT_MINB) weights_kernel(const uint8_t* __restrict__ guide, int64_t gstep, int64_t gframe,
                                                       int w, int h, int pitch, int rowpitch, const float* __restrict__ lut,
                                                       float* __restrict__ chor, float* __restrict__ cvert, int64_t wframe, int vstrip)
 {
