@@ -127,9 +127,9 @@ __global__ void __launch_bounds__(BM_T) bm_kernel(const BmArgs a0, const BmArgs 
     const int lpitch = P.lpitch, rw = P.rw, wc = P.wc;
     uint8_t* Ls = bsm;                                         // [rows][lpitch]
     uint8_t* Rs = Ls + (size_t)(BM_RB + wsz - 1) * lpitch;     // [rows][rw]
-    uint32_t* V2 = (uint32_t*)(Rs + (size_t)(BM_RB + wsz - 1) * rw);   // [np][wc] packed pairs of 16-bit sums, column fastest
+    uint32_t* V2 = (uint32_t*)(((uintptr_t)(Rs + (size_t)(BM_RB + wsz - 1) * rw) + 7) & ~(uintptr_t)7);   // [np][wc] packed pairs of 16-bit sums, column fastest (8-byte aligned: wc is even)
     int* T = (int*)(V2 + (size_t)P.np * wc);                   // [wc] vertical texture sums
-    int2* red = (int2*)(((uintptr_t)(T + wc) + 7) & ~(uintptr_t)7);   // [BM_T] (minsad, mind) per thread
+    int* red = (int*)(((uintptr_t)(T + wc) + 7) & ~(uintptr_t)7);     // [2][BM_T] best key (SAD << 8 | d) per thread for its two pixels
     const uint8_t* Lg = a.left + (size_t)frame * a.l_frame;
     const uint8_t* Rg = a.right + (size_t)frame * a.r_frame;
     int16_t* Dg = a.disp + (size_t)frame * a.d_frame;
@@ -192,7 +192,9 @@ __global__ void __launch_bounds__(BM_T) bm_kernel(const BmArgs a0, const BmArgs 
     }
 
     const int xq = tid & (BM_TW - 1), q = tid / BM_TW;         // phase C: output column of the tile, quarter of the d range
-    const int dq0 = q * (ndisp / 4), dq1 = dq0 + ndisp / 4;    // candidates of this quarter (multiples of 4)
+    const int dq0 = q * (ndisp / 4), dq1 = dq0 + ndisp / 4;    // candidates of this quarter (multiples of 4): uniqueness rescan
+    const int xp = tid & 31, dg = tid >> 5;                    // phase C: pixel pair of the tile, eighth of the d range
+    const int dg0 = dg * (ndisp >> 3), dg1 = dg0 + (ndisp >> 3);   // (multiples of 2: ndisp % 16 == 0)
     auto sad_at = [&](int x, int d) {                          // SAD of candidate d at tile column x from the published sums
         const uint32_t* p = V2 + (d >> 1) * wc + x;
         int s = 0;
@@ -226,32 +228,49 @@ __global__ void __launch_bounds__(BM_T) bm_kernel(const BmArgs a0, const BmArgs 
             }
         }
         __syncthreads();
-        // C. first minimum over this quarter's candidates
-        int minsad = 0x7fffffff, mind = -1;
+        // C. thread (xp, dg): the pixel pair (2 xp, 2 xp + 1) and the dg-th eighth of the candidates.  The two window sums
+        //    share all but one column, so one set of 64-bit loads (wsz + 1 consecutive words) serves both.  key = SAD << 8 | d:
+        //    its integer minimum is the smallest SAD and, among equal SADs, the first candidate.
+        int key0 = 0x7fffffff, key1 = 0x7fffffff;
         {
-            const uint32_t* p = V2 + (dq0 >> 1) * wc + xq;
-            for (int d = dq0; d < dq1; d += 2, p += wc) {
-                uint32_t s2 = 0;                                // both 16-bit halves at once (no carry: see B)
+            const uint32_t* p = V2 + (dg0 >> 1) * wc + 2 * xp;
+            for (int d = dg0; d < dg1; d += 2, p += wc) {
+                uint32_t sa, sb;                                // both 16-bit halves at once (no carry: see B)
                 if (WSZ) {
+                    uint32_t wv[(WSZ ? WSZ : 1) + 1];
 #pragma unroll
-                    for (int k = 0; k < (WSZ ? WSZ : 1); ++k) s2 += p[k];
+                    for (int k = 0; k < ((WSZ ? WSZ : 1) + 1) / 2; ++k) { const uint2 t2 = *(const uint2*)(p + 2 * k); wv[2 * k] = t2.x; wv[2 * k + 1] = t2.y; }
+                    uint32_t mid = 0;
+#pragma unroll
+                    for (int k = 1; k < (WSZ ? WSZ : 1); ++k) mid += wv[k];
+                    sa = mid + wv[0]; sb = mid + wv[WSZ ? WSZ : 1];
                 } else {
-                    for (int k = 0; k < wsz; ++k) s2 += p[k];
+                    sa = 0;
+                    for (int k = 0; k < wsz; ++k) sa += p[k];
+                    sb = sa - p[0] + p[wsz];                    // every half of sa contains the half of p[0]: no borrow
                 }
-                const int s0 = (int)(s2 & 0xffffu), s1 = (int)(s2 >> 16);
-                if (s0 < minsad) { minsad = s0; mind = d; }
-                if (s1 < minsad) { minsad = s1; mind = d + 1; }
+                const int ka0 = (int)(((sa << 8) & 0x00ffff00u) | (uint32_t)d), ka1 = (int)(((sa >> 8) & 0x00ffff00u) | (uint32_t)(d + 1));
+                const int kb0 = (int)(((sb << 8) & 0x00ffff00u) | (uint32_t)d), kb1 = (int)(((sb >> 8) & 0x00ffff00u) | (uint32_t)(d + 1));
+                key0 = min(key0, min(ka0, ka1));
+                key1 = min(key1, min(kb0, kb1));
             }
         }
-        red[tid] = make_int2(minsad, mind);
+        red[tid] = key0; red[BM_T + tid] = key1;
         __syncthreads();
         // D. merge the quarters (ascending d, strict <: the first minimum wins), tests, sub-pixel fit, store
         const int xrel = x0 + xq, xabs = P.lofs + xrel, y = yb + yo;
         bool filtered = false;
         int best = 0x7fffffff, bd = -1;
-        if (q == 0 && xrel < P.width1) {
+        auto merged_key = [&](int x) {                             // best key of tile pixel x over the eight candidate groups
+            const int* r = red + (x & 1) * BM_T + (x >> 1);
+            int m = r[0];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) { const int2 m = red[xq + k * BM_TW]; if (m.x < best) { best = m.x; bd = m.y; } }
+            for (int g8 = 1; g8 < 8; ++g8) m = min(m, r[g8 * 32]);
+            return m;
+        };
+        if (q == 0 && xrel < P.width1) {
+            const int m = merged_key(xq);
+            best = m >> 8; bd = m & 0xff;
             if (want_tex) {
                 int ts = 0;
                 for (int c = xq; c < xq + wsz; ++c) ts += T[c];
@@ -260,17 +279,16 @@ __global__ void __launch_bounds__(BM_T) bm_kernel(const BmArgs a0, const BmArgs 
         }
         if (a.uniq > 0) {
             // every quarter rescans its candidates against the merged minimum (uniform branch: a.uniq is a kernel argument)
-            int gb = 0x7fffffff, gd = -1;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) { const int2 m = red[xq + k * BM_TW]; if (m.x < gb) { gb = m.x; gd = m.y; } }
+            const int mk = merged_key(xq);
+            const int gb = mk >> 8, gd = mk & 0xff;
             const int thresh = gb + gb * a.uniq / 100;
             int hit = 0;
             for (int d = dq0; d < dq1; ++d)
                 if ((d < gd - 1 || d > gd + 1) && sad_at(xq, d) <= thresh) { hit = 1; break; }
             __syncthreads();
-            red[tid] = make_int2(hit, 0);
+            red[tid] = hit;
             __syncthreads();
-            if (q == 0) filtered |= (red[xq].x | red[xq + BM_TW].x | red[xq + 2 * BM_TW].x | red[xq + 3 * BM_TW].x) != 0;
+            if (q == 0) filtered |= (red[xq] | red[xq + BM_TW] | red[xq + 2 * BM_TW] | red[xq + 3 * BM_TW]) != 0;
         }
         if (q == 0 && xrel < P.width1) {
             int val = FILTERED;
