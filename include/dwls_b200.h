@@ -18,7 +18,8 @@
  * back to exceptions.  There is NO CPU fallback: without a CUDA device every compute entry
  * point fails with DWLS_CUDA_ERROR.
  *
- * Threading: one ctx = one CUDA device + one stream + one workspace; use one ctx per host
+ * Threading: one ctx = one CUDA device + its streams + one workspace; calls on one ctx from different CUDA streams are ordered
+ * by the library (each call waits for the previous call's work), they do not run concurrently; use one ctx per host
  * thread (the reference's filter objects are not re-entrant either, fgs_filter.cpp:198-223).
  */
 #ifndef DWLS_B200_H
@@ -108,7 +109,7 @@ DWLS_API dwls_status dwls_set_group_frames(dwls_ctx* ctx, int frames);
  * out16s: CV_16SC1 at view size, caller-allocated.  conf32f: optional CV_32FC1 at view size
  * (getConfidenceMap, 138/274).  roi_out: the disparity-resolution ROI used (getROI, 139).
  * Copies H2D, runs the kernels, copies D2H, synchronises.  The buffers may be ordinary pageable memory: transfers of more
- * than 2 MB are staged through pinned memory by four short-lived host threads of the library (each with its own copy
+ * than 2 MB are staged through pinned memory by four worker threads the context keeps (started on first use, parked between calls) (each with its own copy
  * stream); smaller ones take the driver's pageable path.  dwls_fgs_host moves its images the same way. */
 DWLS_API dwls_status dwls_filter_host(dwls_ctx* ctx,
                                       const dwls_image* disp_left, const dwls_image* disp_right,
