@@ -79,7 +79,10 @@ __global__ void __launch_bounds__(256) bm_prefilter_kernel(const PrefArgs a)
 // (column | offset of the right view's bytes in a staged row | index of the pair of sums in V2).
 // grid = (ceil(width1 / BM_TW), ceil(valid rows / BM_RB), frames * 2 views), block = 256
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int BM_TW = 64, BM_RB = 32, BM_T = 256;
+#ifndef DWLS_BM_RB
+#define DWLS_BM_RB 32
+#endif
+constexpr int BM_TW = 64, BM_RB = DWLS_BM_RB, BM_T = 256;      // BM_RB: rows per band (each band re-does wsz - 1 warm-up rows)
 constexpr int BM_MAXG = 16;      // (c, 4 d) groups a thread may own: (BM_TW + wsz - 1) * ndisp / 4 / BM_T <= BM_MAXG
 
 struct BmPlan { int lofs, rofs, width1, y0, y1, xmin, xmax, wc, np, rw, lpitch; size_t smem; bool ok; };
