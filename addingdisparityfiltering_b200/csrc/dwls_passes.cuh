@@ -20,6 +20,9 @@ struct SolveArgs {
     const float* in[MAXS];   // S planes (frame 0)
     float* out[MAXS];
     int64_t p_frame;         // floats between frames of a plane
+    // first row pass only: plane s may be read from somewhere with its own strides (the exported confidence map standing in
+    // for plane c); 0 = p_frame / pitch.  Rows there must be 16-byte aligned and hold `pitch` readable floats.
+    int64_t in_frame[MAXS]; int in_pitch[MAXS];
     int pitch;               // floats between rows, multiple of 8, shared by all workspace planes
     int w, h;
     float lam;
@@ -141,7 +144,7 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : DWLS_H
         else
 #pragma unroll
             for (int s = 0; s < S; ++s)
-                bulk_g2s(dst + (size_t)(1 + s) * a.pitch, a.in[s] + (size_t)frame * a.p_frame + (size_t)row * a.pitch, row_bytes, bar);
+                bulk_g2s(dst + (size_t)(1 + s) * a.pitch, a.in[s] + (size_t)frame * (a.in_frame[s] ? a.in_frame[s] : a.p_frame) + (size_t)row * (a.in_pitch[s] ? a.in_pitch[s] : a.pitch), row_bytes, bar);
     };
 
     if (t == 0) {
