@@ -378,11 +378,11 @@ static bool plan_solver(int w, int h, SolvePlan* p)
     return true;
 }
 
-template <int S, int MAXT, int HM, bool IL = false>
+template <int S, int MAXT, int HM, bool IL = false, bool DC = false>
 static dwls_status launch_h_inst(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& pl, int frames, cudaStream_t st)
 {
     const size_t smem = hsolve_smem_bytes<S, HM>(pl.hK, a.pitch);
-    auto k = hsolve_kernel<S, MAXT, HM, IL>;
+    auto k = hsolve_kernel<S, MAXT, HM, IL, DC>;
     if (smem > 227 * 1024) return fail(ctx, DWLS_UNSUPPORTED, "row too wide for the shared-memory stages of the row pass");
     dwls_ctx::HCache& hc = ctx->hcache[(const void*)k];
     if (!hc.ctas_per_sm || hc.K != pl.hK || hc.smem != smem) {
@@ -407,6 +407,10 @@ static dwls_status launch_h(dwls_ctx* ctx, const SolveArgs& a, const SolvePlan& 
     if (a.il) {
         if constexpr (S == 2) { if (pl.hM == 8) return launch_h_inst<2, 256, 8, true>(ctx, a, pl, frames, st); }
         return fail(ctx, DWLS_CUDA_ERROR, "internal: interleaved planes need two planes and rows of at most 2048 pixels");
+    }
+    if (a.dl16) {
+        if constexpr (S == 2) { if (pl.hM == 8) return launch_h_inst<2, 256, 8, false, true>(ctx, a, pl, frames, st); }
+        return fail(ctx, DWLS_CUDA_ERROR, "internal: the d*c-forming row pass needs two planes and rows of at most 2048 pixels");
     }
     if (pl.hM == 8) return launch_h_inst<S, 256, 8>(ctx, a, pl, frames, st);          // w <= 2048
     if (pl.hK <= 256) return launch_h_inst<S, 256, 16>(ctx, a, pl, frames, st);       // w <= 4096
@@ -576,6 +580,7 @@ static dwls_status run_sweeps(dwls_ctx* ctx, SolveArgs a, const float* chor, con
         dwls_status s = (S == 1) ? launch_h<1>(ctx, a, pl, frames, st) : launch_h<2>(ctx, a, pl, frames, st);
         if (s) return s;
         for (int k = 0; k < S; ++k) { a.in[k] = a.out[k]; a.in_frame[k] = 0; a.in_pitch[k] = 0; }   // only the first row pass may read from elsewhere
+        a.dl16 = nullptr;
         a.weight = cvert;
         const bool last = (n == num_iter - 1);
         if (pl.vT) {
@@ -791,6 +796,11 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
     const bool alias_c = conf && g.same && !mask_only && !il && cexp && conf_alias_enabled() &&
                          (((uintptr_t)(cexp + (size_t)g.ry * cstep_e + g.rx)) & 15) == 0 && (cstep_e & 3) == 0 && (nf == 1 || (cframe_e & 3) == 0) &&
                          g.rx + g.pitch <= g.dw && cstep_e < ((int64_t)1 << 30);
+    // ... and with 16-byte aligned ROI rows in the left disparity map (and rows of at most 2048 pixels) the first row pass also
+    // forms plane d*c = c * float(L) itself instead of reading what the confidence kernel would have written (another 11.4 MB)
+    const int64_t dstep_e = b->dl_step / 2, dframe_e = b->dl_frame / 2;
+    const bool form_dc = alias_c && g.plan.hM == 8 && !g.plan.vT && (((uintptr_t)(dl + (size_t)g.ry * dstep_e + g.rx)) & 15) == 0 && (dstep_e & 7) == 0 &&
+                         (nf == 1 || (dframe_e & 7) == 0);
     if (conf) {
         dwls_status s2;
         ConfArgs a;
@@ -809,7 +819,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
         if (mask_only) { a.conf = nullptr; a.plane_dc = nullptr; a.plane_c = nullptr; }
         a.p_frame = L.plane; a.pitch = g.pitch; a.il = il;
         a.mask = mask; a.mask_step = mask_step;
-        a.skip_c = alias_c ? 1 : 0;
+        a.skip_c = alias_c ? 1 : 0; a.skip_dc = form_dc ? 1 : 0;
         if ((s2 = launch_conf(ctx, a, nf, st))) return s2;
         if (a.conf || a.mask) {          // zero the exported map (and the mask) outside the ROI (disparity_filters.cpp:187)
             BorderArgs ba;
@@ -857,6 +867,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
     a.w_frame = L.plane; a.p_frame = L.plane; a.pitch = g.pitch; a.w = g.fw; a.h = g.fh;
     a.in[0] = p0; a.out[0] = p0; a.in[1] = p1; a.out[1] = p1; a.il = il;
     if (alias_c) { a.in[1] = cexp + (size_t)g.ry * cstep_e + g.rx; a.in_frame[1] = cframe_e; a.in_pitch[1] = (int)cstep_e; }
+    if (form_dc) { a.dl16 = dl + (size_t)g.ry * dstep_e + g.rx; a.dl16_frame = dframe_e; a.dl16_step = dstep_e; }
     a.out16 = out + (size_t)g.fy * (b->out_step / 2) + g.fx; a.out16_step = b->out_step / 2; a.out16_frame = b->out_frame / 2;
     return run_sweeps(ctx, a, chor, cvert, conf ? 2 : 1, conf ? FIN_WLS : FIN_S16, g.plan, nf, p->lambda, p->lambda_attenuation, p->num_iter, st, &T);
 }

@@ -29,6 +29,7 @@ struct ConfArgs {
     int il;                                           // planes interleaved sector by sector in ONE array at plane_dc (SolveArgs::il): d*c is plane 0, c plane 1
     uint8_t* mask; int64_t mask_step;                 // optional LRC decision export (frame 0 only)
     int skip_c;                                       // the exported map doubles as plane c (the first row pass reads it there): do not write plane_c
+    int skip_dc;                                      // the first row pass forms d*c itself from the map and the left disparities: do not write plane_dc
 };
 
 // offset of (frame, row y, column c, plane s) in a solver plane pair, c = first column of an aligned run of <= 8 (SolveArgs::il)
@@ -187,10 +188,10 @@ __global__ void __launch_bounds__(CF_T, 3) conf_kernel(const ConfArgs a)
                     float* PD = a.plane_dc + plane_off(a.il, a.p_frame, a.pitch, frame, y, cx0, 0);
                     if (nvalid == 8) {
                         if (!a.skip_c) { *(float4*)PC = make_float4(cv[0], cv[1], cv[2], cv[3]); *((float4*)PC + 1) = make_float4(cv[4], cv[5], cv[6], cv[7]); }
-                        *(float4*)PD = make_float4(dc[0], dc[1], dc[2], dc[3]); *((float4*)PD + 1) = make_float4(dc[4], dc[5], dc[6], dc[7]);
+                        if (!a.skip_dc) { *(float4*)PD = make_float4(dc[0], dc[1], dc[2], dc[3]); *((float4*)PD + 1) = make_float4(dc[4], dc[5], dc[6], dc[7]); }
                     } else
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) if (i < nvalid) { if (!a.skip_c) PC[i] = cv[i]; PD[i] = dc[i]; }
+                        for (int i = 0; i < 8; ++i) if (i < nvalid) { if (!a.skip_c) PC[i] = cv[i]; if (!a.skip_dc) PD[i] = dc[i]; }
                 }
                 if (a.conf) {
                     float* E = a.conf + (size_t)frame * a.conf_frame + (size_t)gy * a.conf_step + gx0;

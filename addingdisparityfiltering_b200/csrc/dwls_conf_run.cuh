@@ -315,10 +315,10 @@ __global__ void __launch_bounds__(CR_T, 4) conf_run_kernel(const ConfArgs a, con
                 float* PD = a.plane_dc + plane_off(a.il, a.p_frame, a.pitch, frame, y, cx0, 0);
                 if (nvalid == 8) {
                     if (!a.skip_c) st_global_v8(PC, cv[0], cv[1], cv[2], cv[3], cv[4], cv[5], cv[6], cv[7]);
-                    st_global_v8(PD, dc[0], dc[1], dc[2], dc[3], dc[4], dc[5], dc[6], dc[7]);
+                    if (!a.skip_dc) st_global_v8(PD, dc[0], dc[1], dc[2], dc[3], dc[4], dc[5], dc[6], dc[7]);
                 } else
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) if (i < nvalid) { if (!a.skip_c) PC[i] = cv[i]; PD[i] = dc[i]; }
+                    for (int i = 0; i < 8; ++i) if (i < nvalid) { if (!a.skip_c) PC[i] = cv[i]; if (!a.skip_dc) PD[i] = dc[i]; }
             }
             if (a.conf) {
                 float* E = a.conf + (size_t)frame * a.conf_frame + (size_t)gy * a.conf_step + gx0;

@@ -23,6 +23,9 @@ struct SolveArgs {
     // first row pass only: plane s may be read from somewhere with its own strides (the exported confidence map standing in
     // for plane c); 0 = p_frame / pitch.  Rows there must be 16-byte aligned and hold `pitch` readable floats.
     int64_t in_frame[MAXS]; int in_pitch[MAXS];
+    // first row pass of the confidence path (hsolve_kernel DC): plane 0 = d*c is FORMED here as c * float(L) from the left
+    // disparity map (at the ROI origin; rows 16-byte aligned, `pitch` readable elements) and plane 1 = c, instead of being read
+    const int16_t* dl16; int64_t dl16_frame, dl16_step;     // elements
     int pitch;               // floats between rows, multiple of 8, shared by all workspace planes
     int w, h;
     float lam;
@@ -117,7 +120,8 @@ __host__ __device__ inline size_t hsolve_smem_bytes(int K, int pitch)
     return sizeof(float) * ((size_t)HST * (1 + S) * pitch + HL2BUF * (size_t)(4 + 2 * S) * l2pad_size(K) + 32 * (2 + S) * HM) + sizeof(uint64_t) * HST;
 }
 
-template <int S, int MAXT, int HM, bool IL = false>
+// DC: see SolveArgs::dl16 - the slot of plane 0 in a stage holds the int16 row of the left disparity map (half of it)
+template <int S, int MAXT, int HM, bool IL = false, bool DC = false>
 __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : DWLS_H16MINB) : 1)) hsolve_kernel(const SolveArgs a, const int rows_total)
 {
     extern __shared__ __align__(128) float sm[];
@@ -138,9 +142,13 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : DWLS_H
     auto issue = [&](int i, int frame, int row) {                 // thread 0 only: fetch my i-th row into stage i % HST
         float* dst = stage0 + (size_t)(i % HST) * (1 + S) * a.pitch;
         uint64_t* bar = full + (i % HST);
-        mbar_arrive_expect_tx(bar, (1 + S) * row_bytes);
+        static_assert(!DC || (S == 2 && HM == 8 && !IL), "DC is the first row pass of the confidence path");
+        mbar_arrive_expect_tx(bar, DC ? 2 * row_bytes + row_bytes / 2 : (1 + S) * row_bytes);
         bulk_g2s(dst, a.weight + (size_t)frame * a.w_frame + (size_t)row * a.pitch, row_bytes, bar);
-        if (IL) bulk_g2s(dst + a.pitch, a.in[0] + (size_t)frame * (S * a.p_frame) + (size_t)row * (S * a.pitch), S * row_bytes, bar);
+        if (DC) {
+            bulk_g2s(dst + a.pitch, a.dl16 + (size_t)frame * a.dl16_frame + (size_t)row * a.dl16_step, row_bytes / 2, bar);
+            bulk_g2s(dst + 2 * (size_t)a.pitch, a.in[1] + (size_t)frame * (a.in_frame[1] ? a.in_frame[1] : a.p_frame) + (size_t)row * (a.in_pitch[1] ? a.in_pitch[1] : a.pitch), row_bytes, bar);
+        } else if (IL) bulk_g2s(dst + a.pitch, a.in[0] + (size_t)frame * (S * a.p_frame) + (size_t)row * (S * a.pitch), S * row_bytes, bar);
         else
 #pragma unroll
             for (int s = 0; s < S; ++s)
@@ -178,11 +186,22 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 256 ? (HM == 8 ? HMINB : DWLS_H
             if (t > 0) aprev = a.lam * st[j0 - 1];
 #pragma unroll
             for (int s = 0; s < S; ++s) {
+                if (DC && s == 0) continue;
                 const float* P = IL ? st + a.pitch + j0 * S + 8 * (s ^ sel) : st + (size_t)(1 + s) * a.pitch + j0;
 #pragma unroll
                 for (int q = 0; q < HM / 4; ++q) {
                     const float4 ff = *(const float4*)(P + 4 * q);
                     f[s][4 * q] = ff.x; f[s][4 * q + 1] = ff.y; f[s][4 * q + 2] = ff.z; f[s][4 * q + 3] = ff.w;
+                }
+            }
+            if (DC) {
+                // d*c = conf .mul( float(disp) )   (disparity_filters.cpp:289-290): one rounding, like the confidence kernel's own product
+                const uint4 L4 = *(const uint4*)((const int16_t*)(st + a.pitch) + j0);
+                const uint32_t lw[4] = { L4.x, L4.y, L4.z, L4.w };
+#pragma unroll
+                for (int k = 0; k < HM; ++k) {
+                    const int Lk = (k & 1) ? ((int)lw[k >> 1] >> 16) : (int)(short)(lw[k >> 1] & 0xffffu);
+                    f[0][k] = __fmul_rn(f[S - 1][k], (float)Lk);
                 }
             }
             if (j0 + HM < a.w) {                                       // chunk strictly inside the row: no masks
