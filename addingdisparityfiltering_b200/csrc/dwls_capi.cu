@@ -793,13 +793,13 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
     // the confidence kernel need not write that plane a second time - the first row pass fetches its rows from the map
     // (7.6 MB per 1080p frame less DRAM traffic).  Needs 16-byte aligned ROI rows in the map and `pitch` readable floats per row.
     const int64_t cstep_e = b->conf_step / 4, cframe_e = b->conf_frame / 4;
-    const bool alias_c = conf && g.same && !mask_only && !il && cexp && conf_alias_enabled() &&
-                         (((uintptr_t)(cexp + (size_t)g.ry * cstep_e + g.rx)) & 15) == 0 && (cstep_e & 3) == 0 && (nf == 1 || (cframe_e & 3) == 0) &&
-                         g.rx + g.pitch <= g.dw && cstep_e < ((int64_t)1 << 30);
+    const bool alias_c = conf && !mask_only && !il && cexp && conf_alias_enabled() &&
+                         (((uintptr_t)(cexp + (size_t)g.fy * cstep_e + g.fx)) & 15) == 0 && (cstep_e & 3) == 0 && (nf == 1 || (cframe_e & 3) == 0) &&
+                         g.fx + g.pitch <= g.W && cstep_e < ((int64_t)1 << 30);      // (full resolution: fx, fy, W are rx, ry, dw)
     // ... and with 16-byte aligned ROI rows in the left disparity map (and rows of at most 2048 pixels) the first row pass also
     // forms plane d*c = c * float(L) itself instead of reading what the confidence kernel would have written (another 11.4 MB)
     const int64_t dstep_e = b->dl_step / 2, dframe_e = b->dl_frame / 2;
-    const bool form_dc = alias_c && g.plan.hM == 8 && !g.plan.vT && (((uintptr_t)(dl + (size_t)g.ry * dstep_e + g.rx)) & 15) == 0 && (dstep_e & 7) == 0 &&
+    const bool form_dc = alias_c && g.same && g.plan.hM == 8 && !g.plan.vT && (((uintptr_t)(dl + (size_t)g.ry * dstep_e + g.rx)) & 15) == 0 && (dstep_e & 7) == 0 &&
                          (nf == 1 || (dframe_e & 7) == 0);
     if (conf) {
         dwls_status s2;
@@ -819,7 +819,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
         if (mask_only) { a.conf = nullptr; a.plane_dc = nullptr; a.plane_c = nullptr; }
         a.p_frame = L.plane; a.pitch = g.pitch; a.il = il;
         a.mask = mask; a.mask_step = mask_step;
-        a.skip_c = alias_c ? 1 : 0; a.skip_dc = form_dc ? 1 : 0;
+        a.skip_c = (alias_c && g.same) ? 1 : 0; a.skip_dc = form_dc ? 1 : 0;
         if ((s2 = launch_conf(ctx, a, nf, st))) return s2;
         if (a.conf || a.mask) {          // zero the exported map (and the mask) outside the ROI (disparity_filters.cpp:187)
             BorderArgs ba;
@@ -842,7 +842,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
         u.x_ratio = g.W / (float)g.dw;
         u.fx = g.fx; u.fy = g.fy; u.fw = g.fw; u.fh = g.fh;
         u.conf = conf ? cexp : nullptr; u.conf_step = b->conf_step / 4; u.conf_frame = b->conf_frame / 4;
-        u.plane_dc = p0; u.plane_c = conf ? p1 : nullptr; u.p_frame = L.plane; u.pitch = g.pitch; u.il = il;
+        u.plane_dc = p0; u.plane_c = conf ? p1 : nullptr; u.p_frame = L.plane; u.pitch = g.pitch; u.il = il; u.skip_c = alias_c ? 1 : 0;
         TIMED(K_UPSCALE, st, upscale_prep_kernel<<<dim3((upscale_groups(g.W, g.fx) + 127) / 128, g.H, nf), 128, 0, st>>>(u));
         CK(cudaGetLastError());
     } else if (!conf) {
@@ -866,7 +866,7 @@ static dwls_status filter_frames(dwls_ctx* ctx, const dwls_batch* b, int f0, int
     memset(&a, 0, sizeof a);
     a.w_frame = L.plane; a.p_frame = L.plane; a.pitch = g.pitch; a.w = g.fw; a.h = g.fh;
     a.in[0] = p0; a.out[0] = p0; a.in[1] = p1; a.out[1] = p1; a.il = il;
-    if (alias_c) { a.in[1] = cexp + (size_t)g.ry * cstep_e + g.rx; a.in_frame[1] = cframe_e; a.in_pitch[1] = (int)cstep_e; }
+    if (alias_c) { a.in[1] = cexp + (size_t)g.fy * cstep_e + g.fx; a.in_frame[1] = cframe_e; a.in_pitch[1] = (int)cstep_e; }
     if (form_dc) { a.dl16 = dl + (size_t)g.ry * dstep_e + g.rx; a.dl16_frame = dframe_e; a.dl16_step = dstep_e; }
     a.out16 = out + (size_t)g.fy * (b->out_step / 2) + g.fx; a.out16_step = b->out_step / 2; a.out16_frame = b->out_frame / 2;
     return run_sweeps(ctx, a, chor, cvert, conf ? 2 : 1, conf ? FIN_WLS : FIN_S16, g.plan, nf, p->lambda, p->lambda_attenuation, p->num_iter, st, &T);

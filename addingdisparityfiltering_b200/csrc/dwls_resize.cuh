@@ -41,6 +41,7 @@ struct UpArgs {
     float* conf; int64_t conf_step, conf_frame;       // exported view-size confidence (may be NULL)
     float* plane_dc; float* plane_c; int64_t p_frame; int pitch;   // plane_c NULL in the no-confidence path
     int il;                                           // planes interleaved sector by sector in ONE array at plane_dc (SolveArgs::il)
+    int skip_c;                                       // the exported map doubles as plane c (first row pass reads it there): plane_c is not written
 };
 
 // grid = (ceil(groups/128), H, frames), block 128: a thread takes 4 consecutive view columns, the groups being aligned
@@ -127,12 +128,12 @@ __global__ void __launch_bounds__(128) upscale_prep_kernel(const UpArgs a)
                            : (size_t)frame * a.p_frame + (size_t)(Y - a.fy) * a.pitch + pc0;
     float* pc = a.il ? a.plane_dc + 8 : a.plane_c;
     if (roi[0] && roi[3]) {
-        if (a.plane_c) *(float4*)(pc + po) = make_float4(cval[0], cval[1], cval[2], cval[3]);
+        if (a.plane_c && !a.skip_c) *(float4*)(pc + po) = make_float4(cval[0], cval[1], cval[2], cval[3]);
         *(float4*)(a.plane_dc + po) = make_float4(dcv[0], dcv[1], dcv[2], dcv[3]);
     } else {
 #pragma unroll
         for (int q = 0; q < 4; ++q)
-            if (roi[q]) { if (a.plane_c) pc[po + q] = cval[q]; a.plane_dc[po + q] = dcv[q]; }
+            if (roi[q]) { if (a.plane_c && !a.skip_c) pc[po + q] = cval[q]; a.plane_dc[po + q] = dcv[q]; }
     }
 }
 
