@@ -552,7 +552,13 @@ def main():
                           "(%.4f ms/step with the brackets, %.4f without)" % (args.steps, ms_bracketed / args.steps, ms_compute / args.steps),
                 "pipeline": {"alg_bytes_per_frame": total_alg, "achieved": total_alg * nloc * args.steps / (ms_compute * 1e-3) / 1e9,
                              "frac": total_alg * nloc * args.steps / (ms_compute * 1e-3) / 1e9 / peak,
-                             "what": "whole step of this rank (all kernels, no gather): algorithmic bytes of its frames / its time"},
+                             "what": "whole step of this rank (all kernels, no gather): algorithmic bytes of its frames / its time",
+                             "bytes_not_moved_per_frame": 10 * n_roi,
+                             "note": "B_alg is SURVEY 8d's fixed count.  The library moves 10 B/ROI pixel less than it: the exported "
+                                     "confidence map doubles as plane c and the first row pass forms d*c from the CV_16S disparity, so "
+                                     "conf_kernel<left+lrc> does not write the two planes (-8 B/px) and the first hsolve_kernel reads "
+                                     "2 instead of 4 B/px of plane 0; time / peak against the bytes actually moved is frac * "
+                                     "(1 - bytes_not_moved / alg_bytes)"},
                 "kernels": {k: {"launches": n, "total_ms": round(t, 4), "share": round(t / ksum, 4),
                                 "us_per_frame": round(t * 1e3 / (nloc * args.steps), 3),
                                 "frac": round(per_alg[k] * per_frame_launches.get(k, 1) * nloc * args.steps / (t * 1e-3) / 1e9 / peak, 3) if k in per_alg else None}
