@@ -205,6 +205,34 @@ def test_confidence_stage_radii_and_alignments(ctx, radius, size):
         assert_s16_parity(got, ref["out"], roi)
 
 
+@pytest.mark.parametrize("radius", [1, 2, 3])
+@pytest.mark.parametrize("size", [(960, 80), (1003, 70)])           # aligned rows (TMA tile path) / odd row length (plain-load path)
+def test_lrc_wide_rois_large_disparities(ctx, radius, size):
+    # LRC check (disparity_filters.cpp:306-341) on ROIs several tiles wide: ROI origins at every residue mod 8 (parity of the
+    # gathered right-disparity words, alignment of the gathered confidences), ROIs ending at the image's right / left edge,
+    # rows with disparities of -64 .. 399 px (right columns far from the pixel's own tile), rows of arbitrary int16 values
+    # (mostly misses).  Written for the shared-memory window variant of the LRC step (exp/lrc_window_mode.patch, dropped:
+    # profiles/README.md); kept because nothing else drives the gathers this far from the tile.
+    w, h = size
+    view, dl, dr, _ = synth.make_artificial_example(w, h, 1, seed=7 * radius + w)
+    rng = np.random.default_rng(radius * 1000 + w)
+    dl = (dl.astype(np.int32) + rng.integers(-40, 40, dl.shape)).astype(np.int16)
+    dr = (dr.astype(np.int32) + rng.integers(-40, 40, dr.shape)).astype(np.int16)
+    dl[10:20] = (rng.integers(-64, 400, (10, w)) * 16).astype(np.int16)          # -64 .. 399 px: partly outside the window
+    dl[30:34] = rng.integers(-32768, 32768, (4, w)).astype(np.int16)             # mostly misses
+    dl[40:44, ::3] = 300 * 16
+    rois = [(0, 0, w, h)] + [(k, 1, w - 2 * k - (k & 1), h - 2) for k in range(1, 9)] + [(w - 416, 3, 416, h - 5), (0, 0, 417, h), (37, 2, 421, 33)]
+    f = A.createDisparityWLSFilterGeneric(True, ctx=ctx)
+    f.setDepthDiscontinuityRadius(radius)
+    for roi in rois:
+        got = f.filter(dl, view, None, dr, roi)
+        ref = O.wls_filter(dl, view, dr, roi=roi, lam=8000.0, sigma=1.0, lrc_thresh=24, disc_radius=radius, want_mask=True)
+        assert ref["rc"] == 0
+        assert (f.lrc_mask(dl, dr, ROI=roi) == ref["mask"]).all(), (radius, roi)
+        assert np.abs(f.getConfidenceMap() - ref["conf"]).max() <= 1e-4, (radius, roi)
+        assert_s16_parity(got, ref["out"], roi)
+
+
 def test_confidence_extreme_values(ctx):
     # |d| up to 32767 / -32768: window sums of squares need more than 32 bits; the LRC sum L + R must not wrap
     w, h = 320, 64
