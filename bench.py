@@ -177,7 +177,7 @@ CPU_NOTE = "kind=reference: the reference's fgs_filter.cpp + disparity_filters.c
            "parallel_for_ over all host threads) against the in-repo OpenCV-core stand-in; boxFilter/resize are the stand-in's"
 
 
-def run_reference(args):
+def run_reference(args, out=sys.stdout):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -200,7 +200,7 @@ def run_reference(args):
         "data": "synthetic", "config": cfg,
         "cpu_baseline": {"value": v, "unit": "Mpix/s", "cores": threads, "kind": cpu_kind(), "sample": sample},
         "e2e": {"value": v, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0, "note": CPU_NOTE}))
+        "gpu_launches": 0, "note": CPU_NOTE}), file=out, flush=True)
 
 
 def cuda_time(torch, fn, reps, warm=3):
@@ -354,7 +354,7 @@ def extras_single_gpu(torch, A, ctx, dev, base, peak):
     return res
 
 
-def main():
+def main(out=sys.stdout):
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -377,7 +377,7 @@ def main():
     ap.add_argument("--no-extras", action="store_true", help="skip single_call / other_configs (tuning runs only)")
     args = ap.parse_args()
     if args.impl == "reference":
-        return run_reference(args)
+        return run_reference(args, out)
 
     import torch
     import addingdisparityfiltering_b200 as A
@@ -594,10 +594,26 @@ def main():
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks}
     if world == 1 and not args.no_extras:
         line.update(extras_single_gpu(torch, A, ctx, dev, base, peak))
-    print(json.dumps(line))
+    print(json.dumps(line), file=out, flush=True)
     if dist is not None:
         dist.destroy_process_group()
 
 
+def _only_the_json_line_on_stdout(fn):
+    """The contract is ONE line on stdout.  Libraries write there too (NCCL prints its version banner on stdout when
+    NCCL_DEBUG is set on the box), so file descriptor 1 points at stderr while the bench runs and is restored for the line."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    real = os.fdopen(saved, "w")
+    py_stdout, sys.stdout = sys.stdout, sys.stderr
+    try:
+        return fn(real)
+    finally:
+        sys.stdout = py_stdout
+        real.flush()
+        os.dup2(real.fileno(), 1)
+
+
 if __name__ == "__main__":
-    main()
+    _only_the_json_line_on_stdout(main)
